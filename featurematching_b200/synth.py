@@ -1,0 +1,81 @@
+"""Synthetic frame-pair features at the matcher boundary.
+
+Random-init weights give zero coarse matches at thr 0.2, so benchmarks and parity
+tests plant correspondences directly in the coarse features: image 1's tokens are
+a permutation of image 0's plus noise.  Everything is rounded to bf16 once, here,
+so the CUDA path and the oracle are fed bit-identical values.
+"""
+import torch
+
+
+def _gen(seed, device):
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    return g
+
+
+def coarse_features(B, N0, N1=None, C=256, noise=0.1, kind="planted", seed=1234,
+                    device="cpu", sigma=1.0, n_dup=50):
+    """Returns (feat_c0 [B,N0,C], feat_c1 [B,N1,C]) as bf16, and perm [B,N1] (int64) with
+    feat_c1[b, j] ~ feat_c0[b, perm[b, j]] (perm is -1 where nothing was planted).
+
+    kind: 'planted' permutation + noise; 'iid' independent features (no matches);
+          'dup' planted plus `n_dup` near-duplicate tokens in image 1 (competition / ties).
+    """
+    N1 = N0 if N1 is None else N1
+    f0 = torch.empty(B, N0, C, device=device)
+    f1 = torch.empty(B, N1, C, device=device)
+    perm = torch.full((B, N1), -1, dtype=torch.int64, device=device)
+    for b in range(B):
+        g = _gen(seed + b, device)
+        f0[b] = torch.randn(N0, C, generator=g, device=device) * sigma
+        if kind == "iid":
+            f1[b] = torch.randn(N1, C, generator=g, device=device) * sigma
+            continue
+        p = torch.randperm(N0, generator=g, device=device)
+        n = min(N0, N1)
+        f1[b] = torch.randn(N1, C, generator=g, device=device) * sigma
+        f1[b, :n] = f0[b, p[:n]] + noise * torch.randn(n, C, generator=g, device=device)
+        perm[b, :n] = p[:n]
+        if kind == "dup":
+            k = min(n_dup, n // 2)
+            src = torch.randperm(n, generator=g, device=device)[: 2 * k]
+            # token src[k + t] of image 1 becomes a near-copy of token src[t]
+            f1[b, src[k:]] = f1[b, src[:k]] + 1e-2 * torch.randn(k, C, generator=g, device=device)
+            perm[b, src[k:]] = perm[b, src[:k]]
+    return f0.to(torch.bfloat16), f1.to(torch.bfloat16), perm
+
+
+def fine_features(B, Cf, Hf, Wf, seed=4321, device="cpu", channels_last=True):
+    """Two fine feature maps [B, Cf, Hf, Wf] bf16 (logical NCHW; NHWC strides when
+    channels_last, which is the layout the gather kernel reads without a transpose)."""
+    out = []
+    for k in range(2):
+        g = _gen(seed + 7919 * k, device)
+        f = torch.randn(B, Cf, Hf, Wf, generator=g, device=device).to(torch.bfloat16)
+        if channels_last:
+            f = f.contiguous(memory_format=torch.channels_last)
+        out.append(f)
+    return out[0], out[1]
+
+
+def hot_path_params(Cc=256, Cf=64, WW=49, seed=99, device="cpu", dtype=torch.float32):
+    """Parameters the hot path owns, drawn the way the reference initialises them:
+    kaiming-normal(fan_out, relu) weights for down_proj / merge_feat
+    (network/module/fine_preprocess.py:27-30) and default nn.Linear init elsewhere."""
+    g = _gen(seed, "cpu")
+
+    def kaiming_out(o, i):
+        return torch.randn(o, i, generator=g) * (2.0 / o) ** .5
+
+    def uniform(shape, fan_in):
+        bound = 1.0 / fan_in ** .5
+        return (torch.rand(*shape, generator=g) * 2 - 1) * bound
+
+    p = {
+        "down_w": kaiming_out(Cf, Cc), "down_b": uniform((Cf,), Cc),
+        "merge_w": kaiming_out(Cf, 2 * Cf), "merge_b": uniform((Cf,), 2 * Cf),
+        "mix_w0": uniform((WW,), WW), "mix_b0": uniform((1,), WW),
+        "mix_w1": uniform((WW,), WW), "mix_b1": uniform((1,), WW),
+    }
+    return {k: v.to(device=device, dtype=dtype) for k, v in p.items()}

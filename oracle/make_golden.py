@@ -1,0 +1,154 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference modules.
+
+TEST INFRASTRUCTURE.  Run in the build container (needs /root/reference):
+
+    python -m oracle.make_golden
+
+Each fixture stores the exact inputs (bf16 features as uint16 bit patterns, fp32
+parameters) and the reference's outputs, so the oracle restatement and the CUDA
+path can both be checked on the GPU box, where the reference itself is absent.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from featurematching_b200 import synth  # noqa: E402
+from oracle import reference_shims  # noqa: E402
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                          "tests", "golden")
+
+
+def bf16_bits(t):
+    return t.to(torch.bfloat16).contiguous().view(torch.int16).numpy().view(np.uint16)
+
+
+def run_reference_coarse(ref, f0, f1, hw_i, hw0_c, hw1_c, cfg):
+    m = ref.CoarseMatching(cfg).eval()
+    data = {"hw0_i": hw_i, "hw1_i": hw_i, "hw0_c": hw0_c, "hw1_c": hw1_c}
+    with torch.no_grad():
+        m(f0.float(), f1.float(), data)
+    return data
+
+
+def coarse_case(ref, name, B, hw0_c, hw1_c, kind, noise, seed, thr=0.2, border=2, sigma=1.0):
+    cfg = dict(reference_shims.default_config()["match_coarse"], thr=thr, border_rm=border)
+    N0, N1 = hw0_c[0] * hw0_c[1], hw1_c[0] * hw1_c[1]
+    f0, f1, _ = synth.coarse_features(B, N0, N1, 256, noise, kind, seed, sigma=sigma)
+    hw_i = (hw0_c[0] * 8, hw0_c[1] * 8)
+    d = run_reference_coarse(ref, f0, f1, hw_i, hw0_c, hw1_c, cfg)
+    np.savez_compressed(
+        os.path.join(GOLDEN_DIR, name + ".npz"),
+        feat_c0=bf16_bits(f0), feat_c1=bf16_bits(f1),
+        hw_i=np.array(hw_i), hw0_c=np.array(hw0_c), hw1_c=np.array(hw1_c),
+        thr=thr, border_rm=border, temperature=cfg["dsmax_temperature"],
+        b_ids=d["b_ids"].numpy(), i_ids=d["i_ids"].numpy(), j_ids=d["j_ids"].numpy(),
+        mconf=d["mconf"].numpy(), mkpts0_c=d["mkpts0_c"].numpy(), mkpts1_c=d["mkpts1_c"].numpy(),
+        gt_mask=d["gt_mask"].numpy(),
+    )
+    print(f"{name}: M={d['b_ids'].numel()}  conf max={d['conf_matrix'].max():.4f}")
+    return f0, f1, d
+
+
+def fine_case(ref, name, hw_c, M, seed):
+    """FinePreprocess + FineMatching of the reference on given (b, i, j)."""
+    cfg = reference_shims.default_config()
+    B = 1
+    hw_f = (hw_c[0] * 4, hw_c[1] * 4)
+    hw_i = (hw_c[0] * 8, hw_c[1] * 8)
+    N = hw_c[0] * hw_c[1]
+    fc0, fc1, _ = synth.coarse_features(B, N, N, 256, 0.1, "planted", seed)
+    ff0, ff1 = synth.fine_features(B, 64, hw_f[0], hw_f[1], seed + 1, channels_last=False)
+    g = torch.Generator().manual_seed(seed + 2)
+    # include the four corner cells so windows hit the zero padding on every side
+    corners = torch.tensor([0, hw_c[1] - 1, N - hw_c[1], N - 1])
+    i_ids = torch.cat([corners, torch.randint(0, N, (M - 4,), generator=g)])
+    j_ids = torch.cat([corners.flip(0), torch.randint(0, N, (M - 4,), generator=g)])
+    b_ids = torch.zeros(M, dtype=torch.int64)
+    p = synth.hot_path_params(seed=seed + 3)
+
+    pre = ref.FinePreprocess(cfg).eval()
+    fin = ref.FineMatching(cfg["fine"]).eval()
+    with torch.no_grad():
+        pre.down_proj.weight.copy_(p["down_w"]); pre.down_proj.bias.copy_(p["down_b"])
+        pre.merge_feat.weight.copy_(p["merge_w"]); pre.merge_feat.bias.copy_(p["merge_b"])
+        fin.mix_feat_0.weight.copy_(p["mix_w0"][None]); fin.mix_feat_0.bias.copy_(p["mix_b0"])
+        fin.mix_feat_1.weight.copy_(p["mix_w1"][None]); fin.mix_feat_1.bias.copy_(p["mix_b1"])
+    mk0 = torch.stack([i_ids % hw_c[1], i_ids // hw_c[1]], 1).float() * 8.0
+    mk1 = torch.stack([j_ids % hw_c[1], j_ids // hw_c[1]], 1).float() * 8.0
+    data = {"hw0_i": hw_i, "hw1_i": hw_i, "hw0_c": hw_c, "hw1_c": hw_c, "hw0_f": hw_f,
+            "hw1_f": hw_f, "b_ids": b_ids, "i_ids": i_ids, "j_ids": j_ids,
+            "mkpts0_c": mk0, "mkpts1_c": mk1}
+    with torch.no_grad():
+        w0, w1 = pre(ff0.float(), ff1.float(), fc0.float(), fc1.float(), data)
+        fin(w0, w1, data)
+    np.savez_compressed(
+        os.path.join(GOLDEN_DIR, name + ".npz"),
+        feat_c0=bf16_bits(fc0), feat_c1=bf16_bits(fc1),
+        feat_f0=bf16_bits(ff0), feat_f1=bf16_bits(ff1),
+        hw_i=np.array(hw_i), hw_c=np.array(hw_c), hw_f=np.array(hw_f),
+        b_ids=b_ids.numpy(), i_ids=i_ids.numpy(), j_ids=j_ids.numpy(),
+        mkpts0_c=mk0.numpy(), mkpts1_c=mk1.numpy(),
+        **{k: v.numpy() for k, v in p.items()},
+        win0=w0.numpy(), win1=w1.numpy(),
+        mkpts0_f=data["mkpts0_f"].numpy(), mkpts1_f=data["mkpts1_f"].numpy(),
+    )
+    print(f"{name}: M={M} win {tuple(w0.shape)} mkpts0_f[0]={data['mkpts0_f'][0].tolist()}")
+
+
+def fine_match_special(ref, name, seed):
+    """FineMatching on engineered windows: one-hot heat-maps, uniform heat-maps, random."""
+    cfg = reference_shims.default_config()
+    g = torch.Generator().manual_seed(seed)
+    M, WW, C = 24, 49, 64
+    win0 = torch.randn(M, WW, C, generator=g).to(torch.bfloat16).float()
+    win1 = torch.randn(M, WW, C, generator=g).to(torch.bfloat16).float()
+    win0[8:16] = 0.0      # mixed1 == bias only and window 0 all-zero -> uniform heat-map 1
+    win1[8:16] = 0.0
+    # one-hot: a single cell of window 1 strongly aligned with mixed0's direction
+    win1[16:24] = 0.0
+    p = synth.hot_path_params(seed=seed + 1)
+    for m in range(16, 24):
+        mixed0 = (p["mix_w0"][:, None] * win0[m]).sum(0) + p["mix_b0"]
+        cell = (m * 11) % WW
+        win1[m, cell] = (mixed0 / mixed0.norm() * 200.0).to(torch.bfloat16).float()
+    fin = ref.FineMatching(cfg["fine"]).eval()
+    with torch.no_grad():
+        fin.mix_feat_0.weight.copy_(p["mix_w0"][None]); fin.mix_feat_0.bias.copy_(p["mix_b0"])
+        fin.mix_feat_1.weight.copy_(p["mix_w1"][None]); fin.mix_feat_1.bias.copy_(p["mix_b1"])
+    mk0 = torch.rand(M, 2, generator=g).mul(300).floor()
+    mk1 = torch.rand(M, 2, generator=g).mul(300).floor()
+    data = {"hw0_i": (512, 640), "hw0_f": (256, 320), "mkpts0_c": mk0, "mkpts1_c": mk1}
+    with torch.no_grad():
+        fin(win0, win1, data)
+    np.savez_compressed(
+        os.path.join(GOLDEN_DIR, name + ".npz"),
+        win0=bf16_bits(win0), win1=bf16_bits(win1), mkpts0_c=mk0.numpy(), mkpts1_c=mk1.numpy(),
+        hw_i=np.array((512, 640)), hw_f=np.array((256, 320)),
+        **{k: v.numpy() for k, v in p.items() if k.startswith("mix")},
+        mkpts0_f=data["mkpts0_f"].numpy(), mkpts1_f=data["mkpts1_f"].numpy(),
+    )
+    print(f"{name}: std range {data['mkpts0_f'][:, 2].min():.3e} .. {data['mkpts0_f'][:, 2].max():.4f}")
+
+
+def main():
+    os.makedirs(GOLDEN_DIR, exist_ok=True)
+    ref = reference_shims.load_reference()
+    torch.set_num_threads(1)  # fixed reduction order
+    coarse_case(ref, "coarse_planted", 2, (8, 10), (8, 10), "planted", 0.1, 11)
+    coarse_case(ref, "coarse_nonsquare", 2, (9, 12), (8, 14), "planted", 0.3, 12)
+    coarse_case(ref, "coarse_iid", 1, (8, 10), (8, 10), "iid", 0.0, 13)
+    coarse_case(ref, "coarse_dup", 1, (10, 12), (10, 12), "dup", 0.2, 14)
+    coarse_case(ref, "coarse_noborder_lowthr", 1, (8, 10), (8, 10), "planted", 0.6, 15,
+                thr=0.05, border=0)
+    coarse_case(ref, "coarse_hot", 1, (8, 10), (8, 10), "planted", 0.5, 16, sigma=3.0)
+    fine_case(ref, "fine_chain", (8, 10), 40, 21)
+    fine_match_special(ref, "fine_match_special", 31)
+
+
+if __name__ == "__main__":
+    main()

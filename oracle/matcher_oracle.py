@@ -1,0 +1,212 @@
+"""CPU restatement of the reference's coarse-to-fine matching head.
+
+TEST INFRASTRUCTURE ONLY (see oracle/__init__.py).  Pure functions over torch CPU
+tensors; `dtype` selects fp32 (the reference's arithmetic) or fp64 (tie / epsilon
+analysis).  Every function cites the reference lines it follows
+(paths relative to /root/reference).
+
+Parity status: PINNED against outputs of the reference itself -- see
+tests/golden/ and oracle/make_golden.py; tests/test_oracle.py re-checks it.
+"""
+import math
+
+import torch
+
+
+# --------------------------------------------------------------------------- coarse
+def coarse_confidence(feat_c0, feat_c1, temperature, dtype=torch.float32):
+    """Dual-softmax confidence matrix.
+
+    network/utils/coarse_matching_new.py:64  both feature sets divided by sqrt(C)
+    network/utils/coarse_matching_new.py:66  sim[n,l,s] = <f0[n,l], f1[n,s]> / temperature
+    network/utils/coarse_matching_new.py:68  conf = softmax(sim, dim=1) * softmax(sim, dim=2)
+    """
+    c = feat_c0.shape[-1]
+    f0 = feat_c0.to(dtype) / c ** .5
+    f1 = feat_c1.to(dtype) / c ** .5
+    sim = torch.einsum("nlc,nsc->nls", f0, f1) / temperature
+    return torch.softmax(sim, 1) * torch.softmax(sim, 2)
+
+
+def interior_mask(h, w, border):
+    """[h*w] bool: cell (r, c) is at least `border` cells from every edge.
+
+    network/utils/coarse_matching_new.py:11-28 (mask_border sets False where any of the
+    four grid coordinates is < b or >= dim - b); b <= 0 leaves everything True.
+    """
+    if border <= 0:
+        return torch.ones(h * w, dtype=torch.bool)
+    r = torch.arange(h).unsqueeze(1).expand(h, w)
+    c = torch.arange(w).unsqueeze(0).expand(h, w)
+    ok = (r >= border) & (r < h - border) & (c >= border) & (c < w - border)
+    return ok.reshape(-1)
+
+
+def coarse_match(feat_c0, feat_c1, hw0_i, hw0_c, hw1_c, thr=0.2, border_rm=2,
+                 temperature=0.1, scale0=None, scale1=None, dtype=torch.float32,
+                 return_conf=False):
+    """Eval-mode CoarseMatching.forward + get_coarse_match.
+
+    network/utils/coarse_matching_new.py:99-102  mask = conf > thr, borders removed
+    network/utils/coarse_matching_new.py:105-106 mutual nearest neighbour on conf (equality)
+    network/utils/coarse_matching_new.py:109-110 torch.where -> lexicographic (b, i, j)
+    network/utils/coarse_matching_new.py:126-134 coarse pixel coordinates, scale = H_img / H_coarse
+    network/utils/coarse_matching_new.py:137-141 gt_mask, m_bids, mconf[mconf != 0]
+    """
+    conf = coarse_confidence(feat_c0, feat_c1, temperature, dtype)
+    h0c, w0c = int(hw0_c[0]), int(hw0_c[1])
+    h1c, w1c = int(hw1_c[0]), int(hw1_c[1])
+    mask = conf > thr
+    mask &= interior_mask(h0c, w0c, border_rm)[None, :, None]
+    mask &= interior_mask(h1c, w1c, border_rm)[None, None, :]
+    mask &= conf == conf.amax(dim=2, keepdim=True)
+    mask &= conf == conf.amax(dim=1, keepdim=True)
+    b_ids, i_ids, j_ids = torch.nonzero(mask, as_tuple=True)
+    mconf = conf[b_ids, i_ids, j_ids]
+
+    scale = hw0_i[0] / h0c
+    s0 = scale * scale0[b_ids] if scale0 is not None else scale
+    s1 = scale * scale1[b_ids] if scale1 is not None else scale
+    mkpts0_c = torch.stack([i_ids % w0c, torch.div(i_ids, w0c, rounding_mode="floor")], 1) * s0
+    mkpts1_c = torch.stack([j_ids % w1c, torch.div(j_ids, w1c, rounding_mode="floor")], 1) * s1
+    out = {
+        "b_ids": b_ids, "i_ids": i_ids, "j_ids": j_ids, "m_bids": b_ids,
+        "gt_mask": mconf == 0, "mconf": mconf[mconf != 0],
+        "mkpts0_c": mkpts0_c, "mkpts1_c": mkpts1_c,
+    }
+    if return_conf:
+        out["conf_matrix"] = conf
+    return out
+
+
+# --------------------------------------------------------------------------- fine: windows
+def gather_windows(feat_f, b_ids, cell_ids, w_c, W=7, stride=4, pad=2, dtype=torch.float32):
+    """Windows of `F.unfold(feat_f, (W, W), stride, padding=pad)` at (b, cell) -> [M, W*W, C].
+
+    network/module/fine_preprocess.py:43-46  unfold + rearrange 'n (c ww) l -> n l ww c'
+    network/module/fine_preprocess.py:49-50  select [b_ids, i_ids]
+    Cell l = r * w_c + c covers fine rows stride*r - pad + dy, cols stride*c - pad + dx
+    (zero outside the map); window cell index ww = dy * W + dx.
+    """
+    B, C, Hf, Wf = feat_f.shape
+    M = b_ids.shape[0]
+    r = torch.div(cell_ids, w_c, rounding_mode="floor")
+    c = cell_ids % w_c
+    dy = torch.arange(W).repeat_interleave(W)
+    dx = torch.arange(W).repeat(W)
+    yy = (stride * r - pad)[:, None] + dy[None, :]          # [M, WW]
+    xx = (stride * c - pad)[:, None] + dx[None, :]
+    inside = (yy >= 0) & (yy < Hf) & (xx >= 0) & (xx < Wf)
+    yy = yy.clamp(0, Hf - 1)
+    xx = xx.clamp(0, Wf - 1)
+    nhwc = feat_f.to(dtype).permute(0, 2, 3, 1)             # [B, Hf, Wf, C]
+    win = nhwc[b_ids[:, None].expand(M, W * W), yy, xx]     # [M, WW, C]
+    return win * inside[..., None].to(dtype)
+
+
+def fine_preprocess(feat_f0, feat_f1, feat_c0, feat_c1, b_ids, i_ids, j_ids,
+                    hw0_c, hw1_c, hw0_f, W=7, params=None, dtype=torch.float32):
+    """FinePreprocess.forward.
+
+    network/module/fine_preprocess.py:34      stride = hw0_f[0] // hw0_c[0]
+    network/module/fine_preprocess.py:37-40   M == 0 -> two empty [0, WW, C_f]
+    network/module/fine_preprocess.py:43-50   windows (see gather_windows); padding fixed at 2
+    network/module/fine_preprocess.py:53-60   if fine_concat_coarse_feat:
+        ctx = down_proj(cat[feat_c0[b, i], feat_c1[b, j]])            [2M, C_f]
+        out = merge_feat(cat[cat[win0, win1], repeat(ctx, ww)], -1)   [2M, WW, C_f]
+    `params` = dict(down_w [Cf, Cc], down_b [Cf], merge_w [Cf, 2Cf], merge_b [Cf]) or None.
+    """
+    stride = int(hw0_f[0]) // int(hw0_c[0])
+    cf = feat_f0.shape[1]
+    if b_ids.shape[0] == 0:
+        z = torch.empty(0, W * W, cf, dtype=dtype)
+        return z, z.clone()
+    win0 = gather_windows(feat_f0, b_ids, i_ids, int(hw0_c[1]), W, stride, 2, dtype)
+    win1 = gather_windows(feat_f1, b_ids, j_ids, int(hw1_c[1]), W, stride, 2, dtype)
+    if params is None:
+        return win0, win1
+    dw, db = params["down_w"].to(dtype), params["down_b"].to(dtype)
+    mw, mb = params["merge_w"].to(dtype), params["merge_b"].to(dtype)
+    tok = torch.cat([feat_c0.to(dtype)[b_ids, i_ids], feat_c1.to(dtype)[b_ids, j_ids]], 0)
+    ctx = torch.nn.functional.linear(tok, dw, db)                       # [2M, Cf]
+    both = torch.cat([win0, win1], 0)                                   # [2M, WW, Cf]
+    cat = torch.cat([both, ctx[:, None, :].expand(-1, W * W, -1)], -1)  # [2M, WW, 2Cf]
+    out = torch.nn.functional.linear(cat, mw, mb)
+    return out[: win0.shape[0]], out[win0.shape[0]:]
+
+
+# --------------------------------------------------------------------------- fine: matching
+def window_grid(W, dtype=torch.float32):
+    """[WW, 2] (x, y) normalised window coordinates, row-major (ww = y * W + x).
+
+    kornia create_meshgrid(W, W, True) as called at
+    network/utils/fine_matching_new.py:66: x_k = (k / (W - 1) - 0.5) * 2.
+    """
+    k = torch.linspace(0, W - 1, W, dtype=dtype)
+    k = (k / (W - 1) - 0.5) * 2
+    gx = k.repeat(W)
+    gy = k.repeat_interleave(W)
+    return torch.stack([gx, gy], -1)
+
+
+def _heat_stats(mixed, window, grid):
+    """Heat-map of a mixed centre descriptor against a window; expectation and std.
+
+    network/utils/fine_matching_new.py:56-60  sim[m, r] = <mixed[m], window[m, r]>, softmax(sim / sqrt(C))
+    network/utils/fine_matching_new.py:63-64  spatial expectation (x, y)
+    network/utils/fine_matching_new.py:69-73  var = E[g^2] - E[g]^2, std = sum_xy sqrt(clamp(var, 1e-10))
+    """
+    c = window.shape[-1]
+    sim = torch.einsum("mc,mrc->mr", mixed, window)
+    heat = torch.softmax(sim * (1.0 / c ** .5), dim=1)
+    coords = torch.stack([(grid[:, 0] * heat).sum(-1), (grid[:, 1] * heat).sum(-1)], -1)
+    var = (grid[None] ** 2 * heat[..., None]).sum(1) - coords ** 2
+    std = torch.sqrt(var.clamp(min=1e-10)).sum(-1)
+    return coords, std
+
+
+def fine_match(win0, win1, mkpts0_c, mkpts1_c, params, hw0_i, hw0_f, dtype=torch.float32):
+    """FineMatching.forward (dual correlate), M > 0.
+
+    network/utils/fine_matching_new.py:50-54  mixed_k[m, c] = sum_r w_k[r] * win_k[m, r, c] + b_k
+    network/utils/fine_matching_new.py:56-57  heat 0: mixed0 vs win1; heat 1: mixed1 vs win0
+    network/utils/fine_matching_new.py:75-76  mkpts_f = mkpts_c + (coords * (W // 2) * scale + W // 2)
+    network/utils/fine_matching_new.py:78-79  cat [x, y, std] -> [M, 3]
+    `params` = dict(mix_w0 [WW], mix_b0 [], mix_w1 [WW], mix_b1 []).
+    M == 0 (fine_matching_new.py:40-48): mkpts*_f = mkpts*_c, expec_f = empty [0, 3].
+    """
+    M, WW, C = win0.shape
+    if M == 0:
+        return mkpts0_c, mkpts1_c
+    W = int(math.sqrt(WW))
+    scale = hw0_i[0] / hw0_f[0]
+    f0, f1 = win0.to(dtype), win1.to(dtype)
+    w0, b0 = params["mix_w0"].to(dtype).reshape(-1), params["mix_b0"].to(dtype).reshape(())
+    w1, b1 = params["mix_w1"].to(dtype).reshape(-1), params["mix_b1"].to(dtype).reshape(())
+    mixed0 = torch.einsum("r,mrc->mc", w0, f0) + b0
+    mixed1 = torch.einsum("r,mrc->mc", w1, f1) + b1
+    grid = window_grid(W, dtype)
+    coords0, std0 = _heat_stats(mixed0, f1, grid)
+    coords1, std1 = _heat_stats(mixed1, f0, grid)
+    half = W // 2
+    p0 = mkpts0_c.to(dtype) + (coords0 * half * scale + half)
+    p1 = mkpts1_c.to(dtype) + (coords1 * half * scale + half)
+    return torch.cat([p0, std0[:, None]], -1), torch.cat([p1, std1[:, None]], -1)
+
+
+# --------------------------------------------------------------------------- whole head
+def match_head(feat_c0, feat_c1, feat_f0, feat_f1, hw0_i, hw0_c, hw1_c, hw0_f,
+               coarse_cfg, pre_params, fine_params, W=7, fine_transformer=None,
+               dtype=torch.float32):
+    """net.forward steps 3-5 (network/net.py:75-83) on given features.  `fine_transformer`
+    is the (out-of-scope) fine LocalFeatureTransformer; None = identity."""
+    out = coarse_match(feat_c0, feat_c1, hw0_i, hw0_c, hw1_c, coarse_cfg["thr"],
+                       coarse_cfg["border_rm"], coarse_cfg["dsmax_temperature"], dtype=dtype)
+    win0, win1 = fine_preprocess(feat_f0, feat_f1, feat_c0, feat_c1, out["b_ids"],
+                                 out["i_ids"], out["j_ids"], hw0_c, hw1_c, hw0_f, W,
+                                 pre_params, dtype)
+    if fine_transformer is not None and win0.shape[0] > 0:
+        win0, win1 = fine_transformer(win0, win1)
+    out["mkpts0_f"], out["mkpts1_f"] = fine_match(win0, win1, out["mkpts0_c"], out["mkpts1_c"],
+                                                  fine_params, hw0_i, hw0_f, dtype)
+    return out
