@@ -1,0 +1,111 @@
+// Shared definitions for the coarse/fine kernels and the C-ABI layer.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include "../../include/fm_b200.h"
+
+namespace fm {
+
+// ---------------------------------------------------------------- coarse-stage tiling
+constexpr int kTileM = 128;      // image-0 tokens per MMA tile (TMEM lanes)
+constexpr int kBlockN = 256;     // image-1 tokens resident per work unit (TMEM columns)
+constexpr int kChunkK = 64;      // bf16 elements per 128-byte swizzle row
+constexpr int kMaxC = 256;       // descriptor channels supported by the resident-B layout
+constexpr int kAStages = 5;      // A-operand ring (16 KB per stage)
+constexpr int kAStageBytes = kTileM * kChunkK * 2;    // 16384
+constexpr int kBChunkBytes = kBlockN * kChunkK * 2;   // 32768
+constexpr int kEpiWarps = 8;
+constexpr int kCoarseThreads = 64 + kEpiWarps * 32;   // TMA warp + MMA warp + 8 epilogue warps
+constexpr int kRowSlots = 4;     // exact-tie capacity per image-0 token
+
+// log2-domain head-room of the per-row exponent reference: p = 2^(t - c_i) with
+// c_i = U_i - kHead2 and U_i >= every score of the row, so p <= 2^kHead2 and sums over up to
+// 2^17 tokens stay finite; a row (column) is "lost" only if its best score is more than
+// 126 + kHead2 log2-units (157 nats) below its Cauchy-Schwarz bound.
+constexpr float kHead2 = 100.0f;
+constexpr float kCandMargin = 0.9f;  // candidate pre-filter uses kCandMargin * thr
+
+// status word layout (int32[8], device): written by the coarse kernels
+enum StatusSlot { kStCount = 0, kStFlags = 1, kStMaxUnitCand = 2, kStLost = 3, kStCandTotal = 4 };
+
+// Upper bound (log2 domain, slightly inflated) on every score of a token with norm n0 against
+// tokens with norm <= maxn1; used identically by the stats and resolve kernels.
+__device__ __forceinline__ float score_bound2(float n0, float maxn1, float a2) {
+    return __fmul_rn(__fmul_rn(__fmul_rn(n0, maxn1), a2), 1.001953125f);
+}
+
+struct CoarseDims {
+    int B, N0, N1, C, KC;      // KC = C / 64
+    int MT, NB;                // M tiles (128 rows), N blocks (256 columns)
+    int S, tiles_per_split;    // M range split into S contiguous pieces per (pair, N block)
+    int num_units;             // B * NB * S
+    int N0pad, N1pad;          // MT * 128, NB * 256
+    int cand_cap;              // candidate records per work unit
+};
+
+struct CoarseWorkspace {
+    // all pointers into the caller's workspace
+    __nv_bfloat16* f0b;   // [B, N0, C] bf16 copy (only if the input was fp32)
+    __nv_bfloat16* f1b;
+    float* norm0;         // [B, N0pad]
+    float* maxnorm;       // [B, 2] (float bits, atomicMax)
+    float* rowpart;       // [B, NB * 2, N0pad]
+    float* colpart;       // [B, S, N1pad]
+    uint2* cand;          // [num_units, cand_cap]  x = row_in_unit << 8 | col_in_block, y = score bits
+    int* unit_count;      // [num_units]
+    float* l2row;         // [B, N0]  log2 sum_j 2^t_ij
+    float* l2col;         // [B, N1]
+    unsigned* rowbest;    // [B, N0]  float bits of best strong confidence
+    unsigned* colbest;    // [B, N1]
+    int* rowcnt;          // [B * N0]
+    int2* rowslot;        // [B * N0, kRowSlots]  (j, conf bits)
+    int* blocksum;        // [ceil(B * N0 / 1024)] + scanned copy
+    size_t zero_begin, zero_bytes;   // region cleared at the start of every call
+    size_t total_bytes;
+};
+
+struct CoarseStatsParams {
+    CoarseDims d;
+    float a2;          // log2(e) / (C * temperature)
+    float cand_thr;    // kCandMargin * thr
+    const float* norm0;
+    const float* maxnorm;
+    float* rowpart;
+    float* colpart;
+    uint2* cand;
+    int* unit_count;
+    int* status;
+};
+
+CoarseDims coarse_dims(int B, int N0, int N1, int C, int cand_per_row, int num_sms);
+CoarseWorkspace coarse_workspace(const CoarseDims& d, bool fp32_input, void* base);
+
+// kernels' host launchers (each returns a cudaError_t from the launch)
+cudaError_t launch_coarse_prep(const void* f0, const void* f1, int dtype, const CoarseDims& d,
+                               const CoarseWorkspace& w, cudaStream_t st);
+cudaError_t launch_coarse_stats_tc(const __nv_bfloat16* f0, const __nv_bfloat16* f1,
+                                   const CoarseStatsParams& p, int num_sms, cudaStream_t st);
+cudaError_t launch_coarse_stats_simt(const __nv_bfloat16* f0, const __nv_bfloat16* f1,
+                                     const CoarseStatsParams& p, cudaStream_t st);
+
+struct CoarseResolveParams {
+    CoarseDims d;
+    float a2, thr;
+    int h0c, w0c, h1c, w1c, border;
+    float scale;
+    const float* scale0;   // optional [B, 2]
+    const float* scale1;
+    int64_t* b_ids; int64_t* i_ids; int64_t* j_ids;
+    float* mconf; float* mkpts0_c; float* mkpts1_c;
+    int capacity;
+    int* status;
+};
+cudaError_t launch_coarse_resolve(const CoarseResolveParams& p, const CoarseWorkspace& w,
+                                  cudaStream_t st);
+
+void set_error(const char* fmt, ...);
+
+}  // namespace fm

@@ -1,0 +1,164 @@
+/* fm_b200.h -- C ABI of the B200-native coarse-to-fine matching head.
+ *
+ * Drop-in boundary for the three hot-path modules of Iheckzza/FeatureMatching
+ * (paths relative to the reference tree):
+ *
+ *   fm_coarse_match  <->  CoarseMatching.forward + get_coarse_match
+ *                         network/utils/coarse_matching_new.py:43-143   (called at network/net.py:75)
+ *   fm_fine_gather   <->  FinePreprocess.forward
+ *                         network/module/fine_preprocess.py:32-62       (called at network/net.py:78)
+ *   fm_fine_match    <->  FineMatching.forward
+ *                         network/utils/fine_matching_new.py:22-79      (called at network/net.py:83)
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless stated;
+ *   - the caller owns all buffers (inputs, outputs, workspace); the library allocates nothing
+ *     on the device and keeps no reference to caller memory after the call's work completes;
+ *   - every call only ENQUEUES work on `stream` (a cudaStream_t passed as void*); results,
+ *     including the match count and the status word, are valid after the stream is synchronised;
+ *   - return value: FM_OK or a negative FM_ERR_* for argument / launch errors detected on the
+ *     host (fm_last_error_string() has the detail).  Conditions only the device can detect
+ *     (capacity overflow, lost dynamic range) are reported in the status word, see below;
+ *   - no CPU fallback exists: without a CUDA device every compute entry point fails.
+ *
+ * The host mirror of the reference interface (same class names, constructor dicts and `data`
+ * keys) is featurematching_b200/modules.py; INTEGRATION.md shows the binding a reference
+ * maintainer adds.
+ */
+#ifndef FM_B200_H_
+#define FM_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FM_B200_VERSION 100 /* 0.1.0 */
+
+/* return codes */
+#define FM_OK 0
+#define FM_ERR_BAD_ARG (-1)
+#define FM_ERR_WORKSPACE (-2) /* workspace too small or misaligned */
+#define FM_ERR_CUDA (-3)      /* a CUDA runtime / driver call failed */
+#define FM_ERR_UNSUPPORTED (-4)
+
+/* element types of feature tensors */
+#define FM_DTYPE_BF16 0
+#define FM_DTYPE_F32 1
+
+/* fine feature-map layouts (logical shape is always [B, C, H, W]) */
+#define FM_LAYOUT_NHWC 0 /* channels-last strides: the layout the gather reads directly */
+#define FM_LAYOUT_NCHW 1 /* what the reference backbone emits; transposed once per call */
+
+/* status word: int32[FM_STATUS_WORDS] on the device, written by fm_coarse_match */
+#define FM_STATUS_WORDS 8
+#define FM_ST_COUNT 0     /* number of matches M (clamped to `capacity`)            */
+#define FM_ST_FLAGS 1     /* bitmask of FM_FLAG_*                                   */
+#define FM_ST_MAX_CAND 2  /* largest per-unit candidate count seen (sizing hint)    */
+#define FM_ST_LOST 3      /* tokens whose soft-max sums left fp32 range             */
+#define FM_ST_CAND_TOTAL 4
+
+#define FM_FLAG_CAND_OVERFLOW 1 /* candidate buffer too small: retry with larger cand_per_row */
+#define FM_FLAG_OUT_OVERFLOW 2  /* more matches than `capacity`                               */
+#define FM_FLAG_TIE_OVERFLOW 4  /* more than 4 exactly tied matches in one row                */
+#define FM_FLAG_RANGE 8         /* FM_ST_LOST > 0: scores span > 157 nats below their bound   */
+
+int fm_version(void);
+const char* fm_last_error_string(void);
+
+/* Number of SMs of the current device (used for grid sizing); <0 on error. */
+int fm_device_sm_count(void);
+
+/* ---------------------------------------------------------------- coarse stage
+ * Bytes of workspace fm_coarse_match needs.  `cand_per_row` sizes the candidate buffers
+ * (records per image-0 token per 256-column block; 4 is ample for thr >= 0.1, the Python shim
+ * grows it when FM_FLAG_CAND_OVERFLOW comes back).  Returns 0 on invalid arguments. */
+size_t fm_coarse_workspace_bytes(int B, int N0, int N1, int C, int feat_dtype, int cand_per_row);
+
+/* Dual-softmax mutual-nearest-neighbour coarse matching of B frame pairs.
+ *
+ *   conf[b,i,j] = softmax_i(s)[b,i,j] * softmax_j(s)[b,i,j],
+ *   s[b,i,j]    = <feat_c0[b,i], feat_c1[b,j]> / (C * temperature)      (coarse_matching_new.py:64-68)
+ *   match (b,i,j) iff conf > thr, both cells >= border_rm from their grid borders, and conf is
+ *   the maximum of its row and of its column                            (coarse_matching_new.py:99-106)
+ *
+ * feat_c0 [B,N0,C], feat_c1 [B,N1,C] contiguous, bf16 or fp32 (fp32 is rounded to bf16 once,
+ * on the device: the contraction is bf16 x bf16 -> fp32).  C must be a multiple of 64, <= 256.
+ * N0 = h0c*w0c, N1 = h1c*w1c.  `scale` = image height / coarse height (coarse_matching_new.py:126);
+ * scale0/scale1: optional [B,2] per-pair multipliers (data['scale0'] / data['scale1']), or NULL.
+ *
+ * Outputs (capacity entries each; sorted lexicographically by (b,i,j) like torch.where):
+ *   b_ids,i_ids,j_ids int64[capacity]; mconf float[capacity]; mkpts0_c,mkpts1_c float[capacity,2]
+ *   (x,y) in pixels; status int32[FM_STATUS_WORDS].
+ * The N0 x N1 score / confidence matrix is never written to memory (eval path only;
+ * data['conf_matrix'] is not produced). */
+int fm_coarse_match(const void* feat_c0, const void* feat_c1, int feat_dtype, int B, int N0, int N1,
+                    int C, int h0c, int w0c, int h1c, int w1c, float temperature, float thr,
+                    int border_rm, float scale, const float* scale0, const float* scale1,
+                    int64_t* b_ids, int64_t* i_ids, int64_t* j_ids, float* mconf, float* mkpts0_c,
+                    float* mkpts1_c, int32_t* status, int capacity, void* workspace,
+                    size_t workspace_bytes, int cand_per_row, void* stream);
+
+/* ---------------------------------------------------------------- fine stage: windows
+ * Transposes a fine map [B,C,H,W] (NCHW, bf16 or fp32) to channels-last bf16 [B,H,W,C]. */
+int fm_fine_to_nhwc_bf16(const void* src, int src_dtype, int B, int C, int H, int W, void* dst,
+                         void* stream);
+
+/* FinePreprocess: W x W windows (stride `stride`, zero padding `pad`) of both fine maps at the
+ * matched coarse cells, optionally merged with the down-projected coarse tokens:
+ *   win_k[m, ww, :] = merge_w[:, :Cf] . window_k[m, ww, :] + merge_w[:, Cf:] . ctx_k[m] + merge_b
+ *   ctx_0[m] = down_w . feat_c0[b, i] + down_b,  ctx_1[m] = down_w . feat_c1[b, j] + down_b
+ *                                                               (fine_preprocess.py:43-60)
+ * feat_f0/feat_f1: channels-last bf16 [B,Hf,Wf,Cf] (FM_LAYOUT_NHWC; use fm_fine_to_nhwc_bf16
+ * first for NCHW input).  feat_c0/feat_c1: [B,N0,Cc]/[B,N1,Cc] bf16 or fp32.
+ * down_w [Cf,Cc], down_b [Cf], merge_w [Cf,2Cf], merge_b [Cf] fp32, or all NULL when
+ * fine_concat_coarse_feat is off.  `count` points at the match count on the device (status word
+ * of fm_coarse_match) so no host round-trip is needed; entries >= *count are not touched.
+ * win0/win1: [capacity, W*W, Cf] in out_dtype.  Cf must be 64, W*W <= 64. */
+int fm_fine_gather(const void* feat_f0, const void* feat_f1, const void* feat_c0,
+                   const void* feat_c1, int featc_dtype, const int64_t* b_ids, const int64_t* i_ids,
+                   const int64_t* j_ids, const int32_t* count, int capacity, int B, int Hf, int Wf,
+                   int Cf, int N0, int N1, int Cc, int w0c, int w1c, int stride, int pad, int W,
+                   const float* down_w, const float* down_b, const float* merge_w,
+                   const float* merge_b, void* win0, void* win1, int out_dtype, void* stream);
+
+/* ---------------------------------------------------------------- fine stage: matching
+ * FineMatching (dual correlate): mixed centre descriptor of each window against the OTHER
+ * image's window, softmax(./sqrt(Cf)), spatial expectation on the [-1,1]^2 window grid, std:
+ *   mkpts0_f[m] = (mkpts0_c[m] + coords0[m] * (W/2) * scale + W/2, std0[m])   (fine_matching_new.py:50-79)
+ * win0/win1 [capacity, WW, Cf] bf16 or fp32; mix_w* [WW], mix_b* [1] fp32;
+ * mkpts*_c float[capacity,2]; outputs float[capacity,3].  `scale` = image height / fine height. */
+int fm_fine_match(const void* win0, const void* win1, int win_dtype, const float* mkpts0_c,
+                  const float* mkpts1_c, const float* mix_w0, const float* mix_b0,
+                  const float* mix_w1, const float* mix_b1, const int32_t* count, int capacity,
+                  int WW, int Cf, float scale, float* mkpts0_f, float* mkpts1_f, void* stream);
+
+/* ---------------------------------------------------------------- test / profiling hooks
+ * Same contract as fm_coarse_match, but the score statistics come from a plain SIMT kernel
+ * instead of the tcgen05 kernel.  Exists so tests can tell a tensor-core plumbing bug from a
+ * resolve bug; never used by the product path. */
+int fm_debug_coarse_match_simt(const void* feat_c0, const void* feat_c1, int feat_dtype, int B,
+                               int N0, int N1, int C, int h0c, int w0c, int h1c, int w1c,
+                               float temperature, float thr, int border_rm, float scale,
+                               const float* scale0, const float* scale1, int64_t* b_ids,
+                               int64_t* i_ids, int64_t* j_ids, float* mconf, float* mkpts0_c,
+                               float* mkpts1_c, int32_t* status, int capacity, void* workspace,
+                               size_t workspace_bytes, int cand_per_row, void* stream);
+
+/* Copies the per-token log2 soft-max sums of the last fm_coarse_match call on this workspace:
+ * l2row float[B*N0], l2col float[B*N1] (device pointers). */
+int fm_debug_coarse_lse(const void* workspace, int B, int N0, int N1, int C, int feat_dtype,
+                        int cand_per_row, float* l2row, float* l2col, void* stream);
+
+/* Times only the coarse statistics kernel (the tcgen05 GEMM + fused dual-softmax sums):
+ * runs it `iters` times on `stream` and returns the mean milliseconds per launch in *ms. */
+int fm_profile_coarse_stats(const void* feat_c0, const void* feat_c1, int B, int N0, int N1, int C,
+                            float temperature, float thr, void* workspace, size_t workspace_bytes,
+                            int cand_per_row, int iters, float* ms, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FM_B200_H_ */
