@@ -11,6 +11,8 @@
 // image-0 tiles stream through a 5-stage TMA ring as the A operand.  Each tile is one
 // 128 x 256 x C tcgen05.mma accumulation into one of two 256-column TMEM buffers.
 //
+// Threads: 12 warps = 3 warpgroups.  Warpgroup 0 is control (warp 0 TMA producer, warp 1 MMA
+// issuer, warp 2 TMEM allocation); it gives its registers to the two epilogue warpgroups.
 // Epilogue (8 warps = 2 warpgroups, warpgroup g owns columns [128 g, 128 g + 128) of every tile;
 // a thread owns one accumulator row = one image-0 token):
 //   t    = a2 * dot                      a2 = log2(e) / (C * temperature)
@@ -110,12 +112,16 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
         tma_prefetch_desc(&tmap0);
         tma_prefetch_desc(&tmap1);
     }
-    if (warp == 1) tmem_alloc<512>(&ctl->tmem_base);
+    if (warp == 2) tmem_alloc<512>(&ctl->tmem_base);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = ctl->tmem_base;
 
+    // Register re-balancing between warpgroups: the control warpgroup keeps 40 registers per
+    // thread, the two epilogue warpgroups grow to 232 (128 live column accumulators each).
+    if (warp < kCtlWarps) {
+    reg_dealloc<40>();
     if (warp == 0) {
         // ===================================================== TMA producer (one lane)
         if (lane == 0) {
@@ -175,12 +181,14 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                 umma_commit(&ctl->b_empty);              // resident block may be overwritten
             }
         }
+    }
     } else {
+        reg_alloc<232>();
         // ===================================================== epilogue: 8 warps, 2 warpgroups
-        const int ew = warp - 2;              // 0..7
+        const int ew = warp - kCtlWarps;      // 0..7
         const int wg = ew >> 2;               // column half
         const int q = warp & 3;               // TMEM lane quarter this warp may access
-        const int et = threadIdx.x - 64;      // 0..255
+        const int et = threadIdx.x - kCtlWarps * 32;   // 0..255
         const uint64_t a2p = pack2(p.a2, p.a2);
         uint32_t tile_it = 0;
         for (int u = blockIdx.x; u < d.num_units; u += gridDim.x) {
@@ -301,7 +309,7 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    if (warp == 1) tmem_dealloc<512>(tmem_base);
+    if (warp == 2) tmem_dealloc<512>(tmem_base);
 }
 
 // ---------------------------------------------------------------- host: tensor maps + launch

@@ -1,0 +1,222 @@
+// K2b -- FineMatching (dual correlate), one warp per match.
+//
+//   mixed_k[c]  = sum_r mix_w_k[r] * win_k[r, c] + mix_b_k                 fine_matching_new.py:50-54
+//   sim_0[r]    = <mixed_0, win_1[r]>,  sim_1[r] = <mixed_1, win_0[r]>     fine_matching_new.py:56-57
+//   heat_k      = softmax(sim_k / sqrt(C))                                 fine_matching_new.py:58-60
+//   coords_k    = E_heat[(x, y)] on the [-1, 1]^2 window grid              fine_matching_new.py:63-66
+//   std_k       = sum_xy sqrt(clamp(E[g^2] - E[g]^2, 1e-10))               fine_matching_new.py:69-73
+//   mkpts_k_f   = mkpts_k_c + (coords_k * (W // 2) * scale + W // 2), std  fine_matching_new.py:75-79
+//
+// HBM-bound: 2 * WW * C * sizeof(T) bytes in, 24 bytes out per match.  Each warp streams its
+// matches through a 2-stage shared-memory ring filled by 1-D bulk async copies (UBLKCP, one per
+// window, completing on an mbarrier), so the next match's 12-25 KB are in flight while the
+// current one is reduced.  Phase A gives a lane two channels (conflict-free row reads), phase B
+// gives a lane one window cell and walks the channels in a rotated order (conflict-free 128-bit
+// reads); the 49-way soft-max / expectation reductions are warp shuffles.
+#include "fm_common.cuh"
+#include "fm_ptx.cuh"
+
+namespace fm {
+
+namespace {
+
+constexpr int kC = 64;           // fine descriptor channels
+constexpr int kMaxWW = 64;
+
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// two channels (2 lane, 2 lane + 1) of window row r
+__device__ __forceinline__ float2 load_pair(const float* w, int r, int lane) {
+    return reinterpret_cast<const float2*>(w)[r * (kC / 2) + lane];
+}
+__device__ __forceinline__ float2 load_pair(const __nv_bfloat16* w, int r, int lane) {
+    return __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(w)[r * (kC / 2) + lane]);
+}
+
+// <mixed, window row r>, channels visited in a per-row rotated order
+__device__ __forceinline__ float row_dot(const float* w, const float* mixed, int r) {
+    const float4* row = reinterpret_cast<const float4*>(w + r * kC);
+    const float4* mx = reinterpret_cast<const float4*>(mixed);
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < kC / 4; ++k) {
+        const int ch = (k + r) & (kC / 4 - 1);
+        const float4 x = row[ch], m = mx[ch];
+        acc = fmaf(x.x, m.x, acc); acc = fmaf(x.y, m.y, acc);
+        acc = fmaf(x.z, m.z, acc); acc = fmaf(x.w, m.w, acc);
+    }
+    return acc;
+}
+__device__ __forceinline__ float row_dot(const __nv_bfloat16* w, const float* mixed, int r) {
+    const uint4* row = reinterpret_cast<const uint4*>(w + r * kC);
+    const float4* mx = reinterpret_cast<const float4*>(mixed);
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < kC / 8; ++k) {
+        const int ch = (k + r) & (kC / 8 - 1);
+        const uint4 raw = row[ch];
+        const float4 m0 = mx[2 * ch], m1 = mx[2 * ch + 1];
+        const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
+        const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
+        const float2 c = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.z));
+        const float2 e = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.w));
+        acc = fmaf(a.x, m0.x, acc); acc = fmaf(a.y, m0.y, acc);
+        acc = fmaf(b.x, m0.z, acc); acc = fmaf(b.y, m0.w, acc);
+        acc = fmaf(c.x, m1.x, acc); acc = fmaf(c.y, m1.y, acc);
+        acc = fmaf(e.x, m1.z, acc); acc = fmaf(e.y, m1.w, acc);
+    }
+    return acc;
+}
+
+// soft-max over the WW cells held as (sa: cell lane, sb: cell lane + 32), then expectation / std
+__device__ __forceinline__ void heat_stats(float sa, float sb, bool has_b, float ga_x, float ga_y, float gb_x,
+                                           float gb_y, float temp, float& ex, float& ey, float& sd) {
+    const float ta = sa * temp, tb = has_b ? sb * temp : -INFINITY;
+    const float mx = warp_max(fmaxf(ta, tb));
+    const float ea = expf(ta - mx), eb = has_b ? expf(tb - mx) : 0.f;
+    const float sum = warp_sum(ea + eb);
+    const float ha = ea / sum, hb = eb / sum;
+    ex = warp_sum(fmaf(ga_x, ha, gb_x * hb));
+    ey = warp_sum(fmaf(ga_y, ha, gb_y * hb));
+    const float vx = warp_sum(fmaf(ga_x * ga_x, ha, gb_x * gb_x * hb)) - ex * ex;
+    const float vy = warp_sum(fmaf(ga_y * ga_y, ha, gb_y * gb_y * hb)) - ey * ey;
+    sd = sqrtf(fmaxf(vx, 1e-10f)) + sqrtf(fmaxf(vy, 1e-10f));
+}
+
+template <typename T, int kWarps>
+__global__ void __launch_bounds__(kWarps * 32) fine_match_kernel(
+    const T* __restrict__ win0, const T* __restrict__ win1, const float* __restrict__ mkpts0_c,
+    const float* __restrict__ mkpts1_c, const float* __restrict__ mix_w0, const float* __restrict__ mix_b0,
+    const float* __restrict__ mix_w1, const float* __restrict__ mix_b1, const int* __restrict__ count,
+    int capacity, int WW, int W, float scale, float* __restrict__ out0, float* __restrict__ out1) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t win_bytes = static_cast<uint32_t>(WW) * kC * sizeof(T);
+    // layout: [kWarps][2 stages][2 windows][win_bytes] | mixed [kWarps][2][64] f32 | weights [2][64] | bars
+    uint8_t* ring = smem + static_cast<size_t>(warp) * 4 * win_bytes;
+    float* fbase = reinterpret_cast<float*>(smem + static_cast<size_t>(kWarps) * 4 * win_bytes);
+    float* mixed = fbase + warp * 2 * kC;
+    float* wts = fbase + kWarps * 2 * kC;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(wts + 2 * kMaxWW) + warp * 2;
+
+    for (int k = threadIdx.x; k < 2 * kMaxWW; k += blockDim.x) {
+        const int r = k & (kMaxWW - 1);
+        wts[k] = r < WW ? (k < kMaxWW ? mix_w0[r] : mix_w1[r]) : 0.f;
+    }
+    if (lane == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    const int M = count ? min(*count, capacity) : capacity;
+    const float b0 = *mix_b0, b1 = *mix_b1;
+    const float temp = rsqrtf(static_cast<float>(kC));   // 1 / sqrt(64) = 0.125 exactly
+    const float half = static_cast<float>(W / 2);
+    const float inv = static_cast<float>(W - 1);
+    // window-grid coordinates of this lane's two cells (kornia create_meshgrid, normalised)
+    const int ra = lane, rb = lane + 32;
+    const bool has_a = ra < WW, has_b = rb < WW;
+    const float ga_x = (static_cast<float>(ra % W) / inv - 0.5f) * 2.f, ga_y = (static_cast<float>(ra / W) / inv - 0.5f) * 2.f;
+    const float gb_x = (static_cast<float>(rb % W) / inv - 0.5f) * 2.f, gb_y = (static_cast<float>(rb / W) / inv - 0.5f) * 2.f;
+
+    const int gw = blockIdx.x * kWarps + warp, nw = gridDim.x * kWarps;
+    auto issue = [&](int stage, int m) {
+        uint8_t* dst = ring + static_cast<size_t>(stage) * 2 * win_bytes;
+        mbar_arrive_expect_tx(&bars[stage], 2 * win_bytes);
+        bulk_g2s(dst, win0 + static_cast<size_t>(m) * WW * kC, win_bytes, &bars[stage]);
+        bulk_g2s(dst + win_bytes, win1 + static_cast<size_t>(m) * WW * kC, win_bytes, &bars[stage]);
+    };
+    if (gw < M && lane == 0) issue(0, gw);
+    uint32_t it = 0;
+    for (int m = gw; m < M; m += nw, ++it) {
+        const int s = it & 1;
+        if (m + nw < M && lane == 0) issue(s ^ 1, m + nw);
+        mbar_wait(&bars[s], (it >> 1) & 1);
+        const T* w0 = reinterpret_cast<const T*>(ring + static_cast<size_t>(s) * 2 * win_bytes);
+        const T* w1 = reinterpret_cast<const T*>(ring + static_cast<size_t>(s) * 2 * win_bytes + win_bytes);
+
+        // ---- phase A: mixed centre descriptors, two channels per lane
+        float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
+        for (int r = 0; r < WW; ++r) {
+            const float2 x0 = load_pair(w0, r, lane), x1 = load_pair(w1, r, lane);
+            const float u0 = wts[r], u1 = wts[kMaxWW + r];
+            a0.x = fmaf(u0, x0.x, a0.x); a0.y = fmaf(u0, x0.y, a0.y);
+            a1.x = fmaf(u1, x1.x, a1.x); a1.y = fmaf(u1, x1.y, a1.y);
+        }
+        reinterpret_cast<float2*>(mixed)[lane] = make_float2(a0.x + b0, a0.y + b0);
+        reinterpret_cast<float2*>(mixed + kC)[lane] = make_float2(a1.x + b1, a1.y + b1);
+        __syncwarp();
+
+        // ---- phase B: one window cell per lane (cells lane and lane + 32)
+        float s0a = 0.f, s0b = 0.f, s1a = 0.f, s1b = 0.f;
+        if (has_a) { s0a = row_dot(w1, mixed, ra); s1a = row_dot(w0, mixed + kC, ra); }
+        if (has_b) { s0b = row_dot(w1, mixed, rb); s1b = row_dot(w0, mixed + kC, rb); }
+        float ex0, ey0, sd0, ex1, ey1, sd1;
+        heat_stats(has_a ? s0a : -INFINITY, s0b, has_b, ga_x, ga_y, gb_x, gb_y, temp, ex0, ey0, sd0);
+        heat_stats(has_a ? s1a : -INFINITY, s1b, has_b, ga_x, ga_y, gb_x, gb_y, temp, ex1, ey1, sd1);
+        if (lane == 0) {
+            const float2 c0 = reinterpret_cast<const float2*>(mkpts0_c)[m];
+            const float2 c1 = reinterpret_cast<const float2*>(mkpts1_c)[m];
+            out0[3 * m + 0] = c0.x + (ex0 * half * scale + half);
+            out0[3 * m + 1] = c0.y + (ey0 * half * scale + half);
+            out0[3 * m + 2] = sd0;
+            out1[3 * m + 0] = c1.x + (ex1 * half * scale + half);
+            out1[3 * m + 1] = c1.y + (ey1 * half * scale + half);
+            out1[3 * m + 2] = sd1;
+        }
+        __syncwarp();   // all lanes done with stage s and `mixed` before they are refilled
+    }
+}
+
+template <typename T, int kWarps>
+cudaError_t launch(const void* win0, const void* win1, const float* mk0, const float* mk1, const float* w0,
+                   const float* b0, const float* w1, const float* b1, const int* count, int capacity, int WW,
+                   float scale, float* out0, float* out1, int num_sms, cudaStream_t st) {
+    const size_t smem = static_cast<size_t>(kWarps) * 4 * WW * kC * sizeof(T) + sizeof(float) * (kWarps * 2 * kC + 2 * kMaxWW) +
+                        sizeof(uint64_t) * kWarps * 2;
+    auto kern = fine_match_kernel<T, kWarps>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    int W = 1;
+    while (W * W < WW) ++W;
+    const int ctas_per_sm = static_cast<int>((227 * 1024) / (smem + 1024));
+    int grid = num_sms * (ctas_per_sm > 0 ? ctas_per_sm : 1);
+    const int need = (capacity + kWarps - 1) / kWarps;
+    if (grid > need) grid = need;
+    if (grid < 1) grid = 1;
+    kern<<<grid, kWarps * 32, smem, st>>>(static_cast<const T*>(win0), static_cast<const T*>(win1), mk0, mk1, w0, b0,
+                                         w1, b1, count, capacity, WW, W, scale, out0, out1);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_fine_match(const void* win0, const void* win1, int dtype, const float* mk0, const float* mk1,
+                              const float* w0, const float* b0, const float* w1, const float* b1, const int* count,
+                              int capacity, int WW, float scale, float* out0, float* out1, int num_sms,
+                              cudaStream_t st) {
+    if (dtype == FM_DTYPE_BF16)
+        return launch<__nv_bfloat16, 8>(win0, win1, mk0, mk1, w0, b0, w1, b1, count, capacity, WW, scale, out0, out1,
+                                        num_sms, st);
+    return launch<float, 4>(win0, win1, mk0, mk1, w0, b0, w1, b1, count, capacity, WW, scale, out0, out1, num_sms, st);
+}
+
+}  // namespace fm

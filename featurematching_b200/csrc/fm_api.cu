@@ -1,0 +1,360 @@
+// C ABI of libfm_b200.so (declared in include/fm_b200.h): argument checks, workspace carving and
+// kernel sequencing.  No device allocation, no host synchronisation, no CPU fallback.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "fm_common.cuh"
+
+namespace fm {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+static int cuda_fail(cudaError_t e, const char* what) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return FM_ERR_CUDA;
+}
+
+static int sm_count() {
+    static int cached = 0;
+    if (cached > 0) return cached;
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
+    cached = n;
+    return n;
+}
+
+// ---------------------------------------------------------------- coarse work decomposition
+// Work unit = (pair, 256-column block, contiguous run of `tiles_per_split` 128-row tiles); units
+// are dealt round-robin to a persistent grid.  S (runs per column block) is chosen to minimise
+// the makespan of that static schedule, charging each unit a fixed overhead (loading the
+// resident block, draining the pipeline, reducing the column sums) of ~1 tile.
+CoarseDims coarse_dims(int B, int N0, int N1, int C, int cand_per_row, int num_sms) {
+    // the schedule search costs a fraction of a millisecond: remember the last shape per thread
+    static thread_local int key[6] = {0, 0, 0, 0, 0, 0};
+    static thread_local CoarseDims cached{};
+    if (key[0] == B && key[1] == N0 && key[2] == N1 && key[3] == C && key[4] == cand_per_row && key[5] == num_sms)
+        return cached;
+    CoarseDims d{};
+    d.B = B; d.N0 = N0; d.N1 = N1; d.C = C; d.KC = C / kChunkK;
+    d.MT = (N0 + kTileM - 1) / kTileM;
+    d.NB = (N1 + kBlockN - 1) / kBlockN;
+    d.N0pad = d.MT * kTileM;
+    d.N1pad = d.NB * kBlockN;
+    if (num_sms < 1) num_sms = 148;
+    const double ovh = 1.0;
+    double best = 1e300;
+    int best_tps = d.MT;
+    int prev_tps = -1;
+    for (int S = 1; S <= d.MT; ++S) {
+        const int tps = (d.MT + S - 1) / S;
+        if (tps == prev_tps) continue;
+        prev_tps = tps;
+        const int Se = (d.MT + tps - 1) / tps;
+        const long long units = 1LL * B * d.NB * Se;
+        const int grid = units < num_sms ? static_cast<int>(units) : num_sms;
+        // CTA c runs units c, c + grid, ...; unit u has tiles(u % Se)
+        const int last_tiles = d.MT - (Se - 1) * tps;
+        double makespan = 0.0;
+        if (units <= 262144) {
+            for (int c = 0; c < grid; ++c) {
+                double load = 0.0;
+                for (long long u = c; u < units; u += grid) load += ovh + ((u % Se) == Se - 1 ? last_tiles : tps);
+                if (load > makespan) makespan = load;
+            }
+        } else {   // many rounds: the average is accurate enough
+            const double per_unit = ovh + static_cast<double>(d.MT) / Se;
+            makespan = per_unit * static_cast<double>((units + grid - 1) / grid);
+        }
+        if (makespan < best * 0.999) { best = makespan; best_tps = tps; }
+    }
+    d.tiles_per_split = best_tps;
+    d.S = (d.MT + best_tps - 1) / best_tps;
+    d.num_units = B * d.NB * d.S;
+    d.cand_cap = cand_per_row * d.tiles_per_split * kTileM;
+    key[0] = B; key[1] = N0; key[2] = N1; key[3] = C; key[4] = cand_per_row; key[5] = num_sms;
+    cached = d;
+    return d;
+}
+
+static size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+CoarseWorkspace coarse_workspace(const CoarseDims& d, bool fp32_input, void* base) {
+    CoarseWorkspace w{};
+    uint8_t* p = static_cast<uint8_t*>(base);
+    size_t off = 0;
+    auto take = [&](size_t bytes) { uint8_t* r = p ? p + off : nullptr; off = align_up(off + bytes); return r; };
+    const size_t B = d.B;
+    // ---- region cleared at the start of every call
+    w.zero_begin = off;
+    w.maxnorm = reinterpret_cast<float*>(take(sizeof(float) * B * 2));
+    w.unit_count = reinterpret_cast<int*>(take(sizeof(int) * d.num_units));
+    w.rowbest = reinterpret_cast<unsigned*>(take(sizeof(unsigned) * B * d.N0));
+    w.colbest = reinterpret_cast<unsigned*>(take(sizeof(unsigned) * B * d.N1));
+    w.rowcnt = reinterpret_cast<int*>(take(sizeof(int) * B * d.N0));
+    w.zero_bytes = off - w.zero_begin;
+    // ---- fully rewritten by every call
+    w.norm0 = reinterpret_cast<float*>(take(sizeof(float) * B * d.N0pad));
+    w.rowpart = reinterpret_cast<float*>(take(sizeof(float) * B * d.NB * 2 * d.N0pad));
+    w.colpart = reinterpret_cast<float*>(take(sizeof(float) * B * d.S * d.N1pad));
+    w.l2row = reinterpret_cast<float*>(take(sizeof(float) * B * d.N0));
+    w.l2col = reinterpret_cast<float*>(take(sizeof(float) * B * d.N1));
+    w.rowslot = reinterpret_cast<int2*>(take(sizeof(int2) * B * d.N0 * kRowSlots));
+    w.blocksum = reinterpret_cast<int*>(take(sizeof(int) * ((B * d.N0 + 1023) / 1024 + 1)));
+    w.cand = reinterpret_cast<uint2*>(take(sizeof(uint2) * static_cast<size_t>(d.num_units) * d.cand_cap));
+    if (fp32_input) {
+        w.f0b = reinterpret_cast<__nv_bfloat16*>(take(sizeof(__nv_bfloat16) * B * d.N0 * d.C));
+        w.f1b = reinterpret_cast<__nv_bfloat16*>(take(sizeof(__nv_bfloat16) * B * d.N1 * d.C));
+    }
+    w.total_bytes = off;
+    return w;
+}
+
+cudaError_t launch_fine_gather(const void* ff0, const void* ff1, const void* fc0, const void* fc1, int featc_dtype,
+                               const int64_t* b_ids, const int64_t* i_ids, const int64_t* j_ids, const int* count,
+                               int capacity, int B, int Hf, int Wf, int N0, int N1, int Cc, int w0c, int w1c,
+                               int stride, int pad, int W, const float* down_w, const float* down_b,
+                               const float* merge_w, const float* merge_b, void* win0, void* win1, int out_dtype,
+                               int num_sms, cudaStream_t st);
+cudaError_t launch_to_nhwc(const void* src, int src_dtype, int B, int C, int H, int W, void* dst, cudaStream_t st);
+cudaError_t launch_fine_match(const void* win0, const void* win1, int dtype, const float* mk0, const float* mk1,
+                              const float* w0, const float* b0, const float* w1, const float* b1, const int* count,
+                              int capacity, int WW, float scale, float* out0, float* out1, int num_sms,
+                              cudaStream_t st);
+
+static bool dtype_ok(int t) { return t == FM_DTYPE_BF16 || t == FM_DTYPE_F32; }
+
+static int check_coarse_args(const void* f0, const void* f1, int dt, int B, int N0, int N1, int C, int h0c, int w0c,
+                             int h1c, int w1c, float temperature, float thr, int capacity, const void* ws,
+                             int cand_per_row) {
+    if (!f0 || !f1 || !ws) { set_error("null pointer argument"); return FM_ERR_BAD_ARG; }
+    if (!dtype_ok(dt)) { set_error("feat_dtype must be FM_DTYPE_BF16 or FM_DTYPE_F32"); return FM_ERR_BAD_ARG; }
+    if (B < 1 || N0 < 1 || N1 < 1 || capacity < 0) { set_error("B, N0, N1 must be >= 1 and capacity >= 0"); return FM_ERR_BAD_ARG; }
+    if (C < 64 || C > kMaxC || C % 64) { set_error("C = %d unsupported: need a multiple of 64 in [64, %d]", C, kMaxC); return FM_ERR_UNSUPPORTED; }
+    if (h0c * w0c != N0 || h1c * w1c != N1) { set_error("N0 != h0c * w0c or N1 != h1c * w1c"); return FM_ERR_BAD_ARG; }
+    if (!(temperature > 0.f)) { set_error("temperature must be > 0"); return FM_ERR_BAD_ARG; }
+    if (!(thr > 0.f) || !(thr < 1.f)) { set_error("thr must be in (0, 1): the candidate bound needs thr > 0"); return FM_ERR_BAD_ARG; }
+    if (cand_per_row < 1 || cand_per_row > 256) { set_error("cand_per_row must be in [1, 256]"); return FM_ERR_BAD_ARG; }
+    if (N0 > (1 << 22) || N1 > (1 << 22)) { set_error("token count too large"); return FM_ERR_UNSUPPORTED; }
+    if ((reinterpret_cast<uintptr_t>(f0) | reinterpret_cast<uintptr_t>(f1) | reinterpret_cast<uintptr_t>(ws)) & 15) {
+        set_error("feature and workspace pointers must be 16-byte aligned");
+        return FM_ERR_BAD_ARG;
+    }
+    return FM_OK;
+}
+
+static int coarse_match_impl(bool simt, const void* feat_c0, const void* feat_c1, int feat_dtype, int B, int N0,
+                             int N1, int C, int h0c, int w0c, int h1c, int w1c, float temperature, float thr,
+                             int border_rm, float scale, const float* scale0, const float* scale1, int64_t* b_ids,
+                             int64_t* i_ids, int64_t* j_ids, float* mconf, float* mkpts0_c, float* mkpts1_c,
+                             int32_t* status, int capacity, void* workspace, size_t workspace_bytes,
+                             int cand_per_row, void* stream) {
+    int rc = check_coarse_args(feat_c0, feat_c1, feat_dtype, B, N0, N1, C, h0c, w0c, h1c, w1c, temperature, thr,
+                               capacity, workspace, cand_per_row);
+    if (rc != FM_OK) return rc;
+    if (!status || (capacity > 0 && (!b_ids || !i_ids || !j_ids || !mconf || !mkpts0_c || !mkpts1_c))) {
+        set_error("null output pointer");
+        return FM_ERR_BAD_ARG;
+    }
+    const int sms = sm_count();
+    if (sms <= 0) { set_error("no CUDA device available (this library has no CPU path)"); return FM_ERR_CUDA; }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool f32 = feat_dtype == FM_DTYPE_F32;
+    const CoarseDims d = coarse_dims(B, N0, N1, C, cand_per_row, sms);
+    if (d.tiles_per_split * kTileM >= (1 << 24)) { set_error("row range per unit too large"); return FM_ERR_UNSUPPORTED; }
+    const CoarseWorkspace w = coarse_workspace(d, f32, workspace);
+    if (w.total_bytes > workspace_bytes) {
+        set_error("workspace too small: need %zu bytes, got %zu", w.total_bytes, workspace_bytes);
+        return FM_ERR_WORKSPACE;
+    }
+    cudaError_t e = cudaMemsetAsync(static_cast<uint8_t*>(workspace) + w.zero_begin, 0, w.zero_bytes, st);
+    if (e != cudaSuccess) return cuda_fail(e, "memset(workspace)");
+    e = cudaMemsetAsync(status, 0, sizeof(int32_t) * FM_STATUS_WORDS, st);
+    if (e != cudaSuccess) return cuda_fail(e, "memset(status)");
+
+    e = launch_coarse_prep(feat_c0, feat_c1, feat_dtype, d, w, st);
+    if (e != cudaSuccess) return cuda_fail(e, "coarse_prep launch");
+    const __nv_bfloat16* f0 = f32 ? w.f0b : static_cast<const __nv_bfloat16*>(feat_c0);
+    const __nv_bfloat16* f1 = f32 ? w.f1b : static_cast<const __nv_bfloat16*>(feat_c1);
+
+    CoarseStatsParams sp{};
+    sp.d = d;
+    sp.a2 = 1.4426950408889634f / (static_cast<float>(C) * temperature);
+    sp.cand_thr = kCandMargin * thr;
+    sp.norm0 = w.norm0; sp.maxnorm = w.maxnorm; sp.rowpart = w.rowpart; sp.colpart = w.colpart;
+    sp.cand = w.cand; sp.unit_count = w.unit_count; sp.status = status;
+    e = simt ? launch_coarse_stats_simt(f0, f1, sp, st) : launch_coarse_stats_tc(f0, f1, sp, sms, st);
+    if (e != cudaSuccess) return cuda_fail(e, simt ? "coarse_stats_simt launch" : "coarse_stats_tc launch");
+
+    CoarseResolveParams rp{};
+    rp.d = d; rp.a2 = sp.a2; rp.thr = thr;
+    rp.h0c = h0c; rp.w0c = w0c; rp.h1c = h1c; rp.w1c = w1c; rp.border = border_rm;
+    rp.scale = scale; rp.scale0 = scale0; rp.scale1 = scale1;
+    rp.b_ids = b_ids; rp.i_ids = i_ids; rp.j_ids = j_ids; rp.mconf = mconf;
+    rp.mkpts0_c = mkpts0_c; rp.mkpts1_c = mkpts1_c; rp.capacity = capacity; rp.status = status;
+    e = launch_coarse_resolve(rp, w, st);
+    if (e != cudaSuccess) return cuda_fail(e, "coarse_resolve launch");
+    return FM_OK;
+}
+
+}  // namespace fm
+
+using namespace fm;
+
+extern "C" {
+
+int fm_version(void) { return FM_B200_VERSION; }
+
+const char* fm_last_error_string(void) { return g_err; }
+
+int fm_device_sm_count(void) { return sm_count(); }
+
+size_t fm_coarse_workspace_bytes(int B, int N0, int N1, int C, int feat_dtype, int cand_per_row) {
+    if (B < 1 || N0 < 1 || N1 < 1 || C < 64 || C > kMaxC || C % 64 || !dtype_ok(feat_dtype) || cand_per_row < 1)
+        return 0;
+    const int sms = sm_count();
+    const CoarseDims d = coarse_dims(B, N0, N1, C, cand_per_row, sms > 0 ? sms : 148);
+    return coarse_workspace(d, feat_dtype == FM_DTYPE_F32, nullptr).total_bytes;
+}
+
+int fm_coarse_match(const void* feat_c0, const void* feat_c1, int feat_dtype, int B, int N0, int N1, int C, int h0c,
+                    int w0c, int h1c, int w1c, float temperature, float thr, int border_rm, float scale,
+                    const float* scale0, const float* scale1, int64_t* b_ids, int64_t* i_ids, int64_t* j_ids,
+                    float* mconf, float* mkpts0_c, float* mkpts1_c, int32_t* status, int capacity, void* workspace,
+                    size_t workspace_bytes, int cand_per_row, void* stream) {
+    return coarse_match_impl(false, feat_c0, feat_c1, feat_dtype, B, N0, N1, C, h0c, w0c, h1c, w1c, temperature, thr,
+                             border_rm, scale, scale0, scale1, b_ids, i_ids, j_ids, mconf, mkpts0_c, mkpts1_c, status,
+                             capacity, workspace, workspace_bytes, cand_per_row, stream);
+}
+
+int fm_debug_coarse_match_simt(const void* feat_c0, const void* feat_c1, int feat_dtype, int B, int N0, int N1, int C,
+                               int h0c, int w0c, int h1c, int w1c, float temperature, float thr, int border_rm,
+                               float scale, const float* scale0, const float* scale1, int64_t* b_ids, int64_t* i_ids,
+                               int64_t* j_ids, float* mconf, float* mkpts0_c, float* mkpts1_c, int32_t* status,
+                               int capacity, void* workspace, size_t workspace_bytes, int cand_per_row, void* stream) {
+    return coarse_match_impl(true, feat_c0, feat_c1, feat_dtype, B, N0, N1, C, h0c, w0c, h1c, w1c, temperature, thr,
+                             border_rm, scale, scale0, scale1, b_ids, i_ids, j_ids, mconf, mkpts0_c, mkpts1_c, status,
+                             capacity, workspace, workspace_bytes, cand_per_row, stream);
+}
+
+int fm_debug_coarse_lse(const void* workspace, int B, int N0, int N1, int C, int feat_dtype, int cand_per_row,
+                        float* l2row, float* l2col, void* stream) {
+    if (!workspace || !l2row || !l2col) { set_error("null pointer argument"); return FM_ERR_BAD_ARG; }
+    const int sms = sm_count();
+    if (sms <= 0) { set_error("no CUDA device available"); return FM_ERR_CUDA; }
+    const CoarseDims d = coarse_dims(B, N0, N1, C, cand_per_row, sms);
+    const CoarseWorkspace w = coarse_workspace(d, feat_dtype == FM_DTYPE_F32, const_cast<void*>(workspace));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    cudaError_t e = cudaMemcpyAsync(l2row, w.l2row, sizeof(float) * B * N0, cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(l2col, w.l2col, sizeof(float) * B * N1, cudaMemcpyDeviceToDevice, st);
+    if (e != cudaSuccess) return cuda_fail(e, "copy lse");
+    return FM_OK;
+}
+
+int fm_profile_coarse_stats(const void* feat_c0, const void* feat_c1, int B, int N0, int N1, int C, float temperature,
+                            float thr, void* workspace, size_t workspace_bytes, int cand_per_row, int iters, float* ms,
+                            void* stream) {
+    if (!feat_c0 || !feat_c1 || !workspace || !ms || iters < 1) { set_error("bad argument"); return FM_ERR_BAD_ARG; }
+    if (C < 64 || C > kMaxC || C % 64) { set_error("C unsupported"); return FM_ERR_UNSUPPORTED; }
+    const int sms = sm_count();
+    if (sms <= 0) { set_error("no CUDA device available"); return FM_ERR_CUDA; }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const CoarseDims d = coarse_dims(B, N0, N1, C, cand_per_row, sms);
+    const CoarseWorkspace w = coarse_workspace(d, false, workspace);
+    if (w.total_bytes > workspace_bytes) { set_error("workspace too small"); return FM_ERR_WORKSPACE; }
+    int32_t* status = reinterpret_cast<int32_t*>(w.blocksum);   // scratch: results are not used
+    cudaError_t e = cudaMemsetAsync(static_cast<uint8_t*>(workspace) + w.zero_begin, 0, w.zero_bytes, st);
+    if (e != cudaSuccess) return cuda_fail(e, "memset");
+    e = launch_coarse_prep(feat_c0, feat_c1, FM_DTYPE_BF16, d, w, st);
+    if (e != cudaSuccess) return cuda_fail(e, "coarse_prep launch");
+    CoarseStatsParams sp{};
+    sp.d = d;
+    sp.a2 = 1.4426950408889634f / (static_cast<float>(C) * temperature);
+    sp.cand_thr = kCandMargin * thr;
+    sp.norm0 = w.norm0; sp.maxnorm = w.maxnorm; sp.rowpart = w.rowpart; sp.colpart = w.colpart;
+    sp.cand = w.cand; sp.unit_count = w.unit_count; sp.status = status;
+    cudaEvent_t ev0, ev1;
+    cudaEventCreate(&ev0);
+    cudaEventCreate(&ev1);
+    const __nv_bfloat16* f0 = static_cast<const __nv_bfloat16*>(feat_c0);
+    const __nv_bfloat16* f1 = static_cast<const __nv_bfloat16*>(feat_c1);
+    e = launch_coarse_stats_tc(f0, f1, sp, sms, st);   // warm-up
+    cudaEventRecord(ev0, st);
+    for (int k = 0; k < iters && e == cudaSuccess; ++k) e = launch_coarse_stats_tc(f0, f1, sp, sms, st);
+    cudaEventRecord(ev1, st);
+    cudaError_t es = cudaEventSynchronize(ev1);
+    float total = 0.f;
+    cudaEventElapsedTime(&total, ev0, ev1);
+    cudaEventDestroy(ev0);
+    cudaEventDestroy(ev1);
+    if (e != cudaSuccess) return cuda_fail(e, "coarse_stats_tc launch");
+    if (es != cudaSuccess) return cuda_fail(es, "coarse_stats_tc run");
+    *ms = total / iters;
+    return FM_OK;
+}
+
+int fm_fine_to_nhwc_bf16(const void* src, int src_dtype, int B, int C, int H, int W, void* dst, void* stream) {
+    if (!src || !dst || B < 1 || C < 2 || C % 2 || H < 1 || W < 1 || !dtype_ok(src_dtype)) {
+        set_error("bad argument to fm_fine_to_nhwc_bf16");
+        return FM_ERR_BAD_ARG;
+    }
+    if (C * 33 * sizeof(float) > 48 * 1024) { set_error("C too large"); return FM_ERR_UNSUPPORTED; }
+    cudaError_t e = launch_to_nhwc(src, src_dtype, B, C, H, W, dst, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "to_nhwc launch");
+    return FM_OK;
+}
+
+int fm_fine_gather(const void* feat_f0, const void* feat_f1, const void* feat_c0, const void* feat_c1, int featc_dtype,
+                   const int64_t* b_ids, const int64_t* i_ids, const int64_t* j_ids, const int32_t* count, int capacity,
+                   int B, int Hf, int Wf, int Cf, int N0, int N1, int Cc, int w0c, int w1c, int stride, int pad, int W,
+                   const float* down_w, const float* down_b, const float* merge_w, const float* merge_b, void* win0,
+                   void* win1, int out_dtype, void* stream) {
+    if (!feat_f0 || !feat_f1 || !b_ids || !i_ids || !j_ids || !win0 || !win1) { set_error("null pointer argument"); return FM_ERR_BAD_ARG; }
+    if (Cf != 64) { set_error("Cf = %d unsupported (fine descriptors have 64 channels)", Cf); return FM_ERR_UNSUPPORTED; }
+    if (W < 2 || W * W > 64) { set_error("window %d unsupported (need 2 <= W and W*W <= 64)", W); return FM_ERR_UNSUPPORTED; }
+    if (capacity < 0 || B < 1 || Hf < 1 || Wf < 1 || w0c < 1 || w1c < 1 || stride < 1 || pad < 0) { set_error("bad size argument"); return FM_ERR_BAD_ARG; }
+    if (!dtype_ok(out_dtype) || !dtype_ok(featc_dtype)) { set_error("bad dtype"); return FM_ERR_BAD_ARG; }
+    const bool merge = down_w != nullptr;
+    if (merge && (!down_b || !merge_w || !merge_b || !feat_c0 || !feat_c1)) { set_error("merge parameters must be all set or all NULL"); return FM_ERR_BAD_ARG; }
+    if (merge && (Cc < 8 || Cc % 8 || Cc > 1024)) { set_error("Cc = %d unsupported", Cc); return FM_ERR_UNSUPPORTED; }
+    if (capacity == 0) return FM_OK;
+    const int sms = sm_count();
+    if (sms <= 0) { set_error("no CUDA device available (this library has no CPU path)"); return FM_ERR_CUDA; }
+    cudaError_t e = launch_fine_gather(feat_f0, feat_f1, feat_c0, feat_c1, featc_dtype, b_ids, i_ids, j_ids, count,
+                                       capacity, B, Hf, Wf, N0, N1, Cc, w0c, w1c, stride, pad, W, down_w, down_b,
+                                       merge_w, merge_b, win0, win1, out_dtype, sms, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "fine_gather launch");
+    return FM_OK;
+}
+
+int fm_fine_match(const void* win0, const void* win1, int win_dtype, const float* mkpts0_c, const float* mkpts1_c,
+                  const float* mix_w0, const float* mix_b0, const float* mix_w1, const float* mix_b1,
+                  const int32_t* count, int capacity, int WW, int Cf, float scale, float* mkpts0_f, float* mkpts1_f,
+                  void* stream) {
+    if (!win0 || !win1 || !mkpts0_c || !mkpts1_c || !mix_w0 || !mix_b0 || !mix_w1 || !mix_b1 || !mkpts0_f || !mkpts1_f) {
+        set_error("null pointer argument");
+        return FM_ERR_BAD_ARG;
+    }
+    if (Cf != 64) { set_error("Cf = %d unsupported (fine descriptors have 64 channels)", Cf); return FM_ERR_UNSUPPORTED; }
+    int W = 1;
+    while (W * W < WW) ++W;
+    if (W * W != WW || W < 2 || WW > 64) { set_error("WW = %d unsupported (need a square window, 4 <= WW <= 64)", WW); return FM_ERR_UNSUPPORTED; }
+    if (!dtype_ok(win_dtype) || capacity < 0) { set_error("bad argument"); return FM_ERR_BAD_ARG; }
+    if (capacity == 0) return FM_OK;
+    const int sms = sm_count();
+    if (sms <= 0) { set_error("no CUDA device available (this library has no CPU path)"); return FM_ERR_CUDA; }
+    cudaError_t e = launch_fine_match(win0, win1, win_dtype, mkpts0_c, mkpts1_c, mix_w0, mix_b0, mix_w1, mix_b1, count,
+                                      capacity, WW, scale, mkpts0_f, mkpts1_f, sms, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "fine_match launch");
+    return FM_OK;
+}
+
+}  // extern "C"

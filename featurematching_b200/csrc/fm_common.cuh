@@ -18,7 +18,8 @@ constexpr int kAStages = 5;      // A-operand ring (16 KB per stage)
 constexpr int kAStageBytes = kTileM * kChunkK * 2;    // 16384
 constexpr int kBChunkBytes = kBlockN * kChunkK * 2;   // 32768
 constexpr int kEpiWarps = 8;
-constexpr int kCoarseThreads = 64 + kEpiWarps * 32;   // TMA warp + MMA warp + 8 epilogue warps
+constexpr int kCtlWarps = 4;     // warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM owner, warp 3 idle
+constexpr int kCoarseThreads = (kCtlWarps + kEpiWarps) * 32;   // 3 warpgroups: control + 2 epilogue
 constexpr int kRowSlots = 4;     // exact-tie capacity per image-0 token
 
 // log2-domain head-room of the per-row exponent reference: p = 2^(t - c_i) with

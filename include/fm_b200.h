@@ -37,6 +37,12 @@ extern "C" {
 
 #define FM_B200_VERSION 100 /* 0.1.0 */
 
+#if defined(__GNUC__)
+#define FM_API __attribute__((visibility("default")))
+#else
+#define FM_API
+#endif
+
 /* return codes */
 #define FM_OK 0
 #define FM_ERR_BAD_ARG (-1)
@@ -65,17 +71,17 @@ extern "C" {
 #define FM_FLAG_TIE_OVERFLOW 4  /* more than 4 exactly tied matches in one row                */
 #define FM_FLAG_RANGE 8         /* FM_ST_LOST > 0: scores span > 157 nats below their bound   */
 
-int fm_version(void);
-const char* fm_last_error_string(void);
+FM_API int fm_version(void);
+FM_API const char* fm_last_error_string(void);
 
 /* Number of SMs of the current device (used for grid sizing); <0 on error. */
-int fm_device_sm_count(void);
+FM_API int fm_device_sm_count(void);
 
 /* ---------------------------------------------------------------- coarse stage
  * Bytes of workspace fm_coarse_match needs.  `cand_per_row` sizes the candidate buffers
  * (records per image-0 token per 256-column block; 4 is ample for thr >= 0.1, the Python shim
  * grows it when FM_FLAG_CAND_OVERFLOW comes back).  Returns 0 on invalid arguments. */
-size_t fm_coarse_workspace_bytes(int B, int N0, int N1, int C, int feat_dtype, int cand_per_row);
+FM_API size_t fm_coarse_workspace_bytes(int B, int N0, int N1, int C, int feat_dtype, int cand_per_row);
 
 /* Dual-softmax mutual-nearest-neighbour coarse matching of B frame pairs.
  *
@@ -94,7 +100,7 @@ size_t fm_coarse_workspace_bytes(int B, int N0, int N1, int C, int feat_dtype, i
  *   (x,y) in pixels; status int32[FM_STATUS_WORDS].
  * The N0 x N1 score / confidence matrix is never written to memory (eval path only;
  * data['conf_matrix'] is not produced). */
-int fm_coarse_match(const void* feat_c0, const void* feat_c1, int feat_dtype, int B, int N0, int N1,
+FM_API int fm_coarse_match(const void* feat_c0, const void* feat_c1, int feat_dtype, int B, int N0, int N1,
                     int C, int h0c, int w0c, int h1c, int w1c, float temperature, float thr,
                     int border_rm, float scale, const float* scale0, const float* scale1,
                     int64_t* b_ids, int64_t* i_ids, int64_t* j_ids, float* mconf, float* mkpts0_c,
@@ -103,7 +109,7 @@ int fm_coarse_match(const void* feat_c0, const void* feat_c1, int feat_dtype, in
 
 /* ---------------------------------------------------------------- fine stage: windows
  * Transposes a fine map [B,C,H,W] (NCHW, bf16 or fp32) to channels-last bf16 [B,H,W,C]. */
-int fm_fine_to_nhwc_bf16(const void* src, int src_dtype, int B, int C, int H, int W, void* dst,
+FM_API int fm_fine_to_nhwc_bf16(const void* src, int src_dtype, int B, int C, int H, int W, void* dst,
                          void* stream);
 
 /* FinePreprocess: W x W windows (stride `stride`, zero padding `pad`) of both fine maps at the
@@ -117,7 +123,7 @@ int fm_fine_to_nhwc_bf16(const void* src, int src_dtype, int B, int C, int H, in
  * fine_concat_coarse_feat is off.  `count` points at the match count on the device (status word
  * of fm_coarse_match) so no host round-trip is needed; entries >= *count are not touched.
  * win0/win1: [capacity, W*W, Cf] in out_dtype.  Cf must be 64, W*W <= 64. */
-int fm_fine_gather(const void* feat_f0, const void* feat_f1, const void* feat_c0,
+FM_API int fm_fine_gather(const void* feat_f0, const void* feat_f1, const void* feat_c0,
                    const void* feat_c1, int featc_dtype, const int64_t* b_ids, const int64_t* i_ids,
                    const int64_t* j_ids, const int32_t* count, int capacity, int B, int Hf, int Wf,
                    int Cf, int N0, int N1, int Cc, int w0c, int w1c, int stride, int pad, int W,
@@ -130,7 +136,7 @@ int fm_fine_gather(const void* feat_f0, const void* feat_f1, const void* feat_c0
  *   mkpts0_f[m] = (mkpts0_c[m] + coords0[m] * (W/2) * scale + W/2, std0[m])   (fine_matching_new.py:50-79)
  * win0/win1 [capacity, WW, Cf] bf16 or fp32; mix_w* [WW], mix_b* [1] fp32;
  * mkpts*_c float[capacity,2]; outputs float[capacity,3].  `scale` = image height / fine height. */
-int fm_fine_match(const void* win0, const void* win1, int win_dtype, const float* mkpts0_c,
+FM_API int fm_fine_match(const void* win0, const void* win1, int win_dtype, const float* mkpts0_c,
                   const float* mkpts1_c, const float* mix_w0, const float* mix_b0,
                   const float* mix_w1, const float* mix_b1, const int32_t* count, int capacity,
                   int WW, int Cf, float scale, float* mkpts0_f, float* mkpts1_f, void* stream);
@@ -139,7 +145,7 @@ int fm_fine_match(const void* win0, const void* win1, int win_dtype, const float
  * Same contract as fm_coarse_match, but the score statistics come from a plain SIMT kernel
  * instead of the tcgen05 kernel.  Exists so tests can tell a tensor-core plumbing bug from a
  * resolve bug; never used by the product path. */
-int fm_debug_coarse_match_simt(const void* feat_c0, const void* feat_c1, int feat_dtype, int B,
+FM_API int fm_debug_coarse_match_simt(const void* feat_c0, const void* feat_c1, int feat_dtype, int B,
                                int N0, int N1, int C, int h0c, int w0c, int h1c, int w1c,
                                float temperature, float thr, int border_rm, float scale,
                                const float* scale0, const float* scale1, int64_t* b_ids,
@@ -149,12 +155,12 @@ int fm_debug_coarse_match_simt(const void* feat_c0, const void* feat_c1, int fea
 
 /* Copies the per-token log2 soft-max sums of the last fm_coarse_match call on this workspace:
  * l2row float[B*N0], l2col float[B*N1] (device pointers). */
-int fm_debug_coarse_lse(const void* workspace, int B, int N0, int N1, int C, int feat_dtype,
+FM_API int fm_debug_coarse_lse(const void* workspace, int B, int N0, int N1, int C, int feat_dtype,
                         int cand_per_row, float* l2row, float* l2col, void* stream);
 
 /* Times only the coarse statistics kernel (the tcgen05 GEMM + fused dual-softmax sums):
  * runs it `iters` times on `stream` and returns the mean milliseconds per launch in *ms. */
-int fm_profile_coarse_stats(const void* feat_c0, const void* feat_c1, int B, int N0, int N1, int C,
+FM_API int fm_profile_coarse_stats(const void* feat_c0, const void* feat_c1, int B, int N0, int N1, int C,
                             float temperature, float thr, void* workspace, size_t workspace_bytes,
                             int cand_per_row, int iters, float* ms, void* stream);
 

@@ -1,0 +1,272 @@
+"""Parity of the CUDA path (through the C ABI of libfm_b200.so) against the oracle and the
+golden fixtures produced by the real reference.  Needs a B200: every test is marked gpu."""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from featurematching_b200 import _lib, modules, synth
+from oracle import compare, matcher_oracle as mo, reference_shims
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+CFG = reference_shims.default_config()
+COARSE_CASES = ["coarse_planted", "coarse_nonsquare", "coarse_iid", "coarse_dup",
+                "coarse_noborder_lowthr", "coarse_hot"]
+
+
+def load(golden_dir, name):
+    return dict(np.load(os.path.join(golden_dir, name + ".npz")))
+
+
+def coarse_module(thr=0.2, border=2, temperature=0.1, simt=False):
+    m = modules.CoarseMatching(dict(CFG["match_coarse"], thr=thr, border_rm=border,
+                                    dsmax_temperature=temperature)).eval()
+    m._debug_simt = simt
+    return m
+
+
+def run_coarse(f0, f1, hw_i, hw0_c, hw1_c, simt=False, **kw):
+    m = coarse_module(simt=simt, **kw)
+    data = {"hw0_i": hw_i, "hw1_i": hw_i, "hw0_c": hw0_c, "hw1_c": hw1_c}
+    m(f0.to(DEV), f1.to(DEV), data)
+    return data
+
+
+# ------------------------------------------------------------------------------ coarse
+@pytest.mark.parametrize("simt", [True, False], ids=["simt", "tcgen05"])
+@pytest.mark.parametrize("name", COARSE_CASES)
+def test_coarse_golden(golden_dir, name, simt):
+    g = load(golden_dir, name)
+    f0, f1 = compare.from_bits(g["feat_c0"]), compare.from_bits(g["feat_c1"])
+    hw_i, hw0_c, hw1_c = tuple(g["hw_i"]), tuple(g["hw0_c"]), tuple(g["hw1_c"])
+    thr = float(g["thr"])
+    d = run_coarse(f0, f1, hw_i, hw0_c, hw1_c, simt, thr=thr, border=int(g["border_rm"]),
+                   temperature=float(g["temperature"]))
+    o64 = mo.coarse_match(f0, f1, hw_i, hw0_c, hw1_c, thr, int(g["border_rm"]),
+                          float(g["temperature"]), dtype=torch.float64, return_conf=True)
+    ref = {k: torch.from_numpy(g[k]) for k in ("b_ids", "i_ids", "j_ids", "mconf", "mkpts0_c", "mkpts1_c")}
+    compare.check_coarse(d, ref, o64["conf_matrix"], thr)
+    assert d["b_ids"].dtype == torch.int64 and d["mconf"].dtype == torch.float32
+    assert d["mkpts0_c"].shape == (d["b_ids"].shape[0], 2)
+    assert d["gt_mask"].dtype == torch.bool and not bool(d["gt_mask"].any())
+    assert d["m_bids"] is d["b_ids"] or torch.equal(d["m_bids"], d["b_ids"])
+    assert "conf_matrix" not in d
+
+
+@pytest.mark.parametrize("shape", [((20, 24), (20, 24), 2, "dup", 0.4),
+                                   ((17, 23), (19, 21), 3, "planted", 0.3),
+                                   ((40, 40), (40, 40), 2, "planted", 0.1),
+                                   ((33, 41), (30, 37), 1, "iid", 0.0)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_coarse_vs_oracle_medium(shape, dtype):
+    hw0_c, hw1_c, B, kind, noise = shape
+    N0, N1 = hw0_c[0] * hw0_c[1], hw1_c[0] * hw1_c[1]
+    f0, f1, _ = synth.coarse_features(B, N0, N1, 256, noise, kind, 77)
+    hw_i = (hw0_c[0] * 8, hw0_c[1] * 8)
+    d = run_coarse(f0.to(dtype), f1.to(dtype), hw_i, hw0_c, hw1_c)
+    o32 = mo.coarse_match(f0, f1, hw_i, hw0_c, hw1_c)
+    o64 = mo.coarse_match(f0, f1, hw_i, hw0_c, hw1_c, dtype=torch.float64, return_conf=True)
+    compare.check_coarse(d, o32, o64["conf_matrix"])
+    if kind != "iid":
+        assert d["b_ids"].numel() > 20
+
+
+@pytest.mark.parametrize("simt", [True, False], ids=["simt", "tcgen05"])
+def test_coarse_lse_matches_oracle(simt):
+    """The fused soft-max denominators themselves (log2 domain), not just the match list."""
+    hw_c = (24, 32)
+    N = hw_c[0] * hw_c[1]
+    f0, f1, _ = synth.coarse_features(2, N, N, 256, 0.3, "planted", 5)
+    m = coarse_module(simt=simt)
+    m.match_raw(f0.to(DEV), f1.to(DEV), (192, 256), hw_c, hw_c)
+    lib = _lib.load()
+    l2r = torch.empty(2 * N, device=DEV)
+    l2c = torch.empty(2 * N, device=DEV)
+    rc = lib.fm_debug_coarse_lse(_lib.ptr(m._ws.buf), 2, N, N, 256, 0, m.cand_per_row,
+                                 _lib.ptr(l2r), _lib.ptr(l2c), _lib.stream_ptr(torch.device(DEV)))
+    _lib.check(rc, "fm_debug_coarse_lse")
+    sim = torch.einsum("nlc,nsc->nls", f0.double() / 16, f1.double() / 16) / 0.1
+    ref_r = torch.logsumexp(sim, 2).reshape(-1) / math.log(2)
+    ref_c = torch.logsumexp(sim, 1).reshape(-1) / math.log(2)
+    assert (l2r.cpu().double() - ref_r).abs().max() < 2e-4
+    assert (l2c.cpu().double() - ref_c).abs().max() < 2e-4
+
+
+def test_coarse_scale_and_ties():
+    """data['scale0'/'scale1'] multipliers, and exact duplicates -> all tied matches kept."""
+    hw_c = (10, 12)
+    N = hw_c[0] * hw_c[1]
+    f0, f1, _ = synth.coarse_features(1, N, N, 256, 0.0, "planted", 9)
+    # exact duplicate rows in image 1: the reference keeps both (equality MNN), conf ~ 0.25 each
+    f1[0, 30] = f1[0, 31]
+    scale0 = torch.tensor([[1.5, 2.0]])
+    scale1 = torch.tensor([[0.5, 3.0]])
+    m = coarse_module(thr=0.2, border=0)
+    data = {"hw0_i": (80, 96), "hw1_i": (80, 96), "hw0_c": hw_c, "hw1_c": hw_c,
+            "scale0": scale0.to(DEV), "scale1": scale1.to(DEV)}
+    m(f0.to(DEV), f1.to(DEV), data)
+    o = mo.coarse_match(f0, f1, (80, 96), hw_c, hw_c, 0.2, 0, 0.1, scale0, scale1)
+    o64 = mo.coarse_match(f0, f1, (80, 96), hw_c, hw_c, 0.2, 0, 0.1, dtype=torch.float64, return_conf=True)
+    compare.check_coarse(data, o, o64["conf_matrix"])
+    assert torch.equal(data["mkpts0_c"].cpu(), o["mkpts0_c"])
+
+
+def test_coarse_full_size_properties():
+    """640x512 (N = 5120) planted pairs: too big for a dense fp64 check of every pair, so check
+    size-independent properties: matches follow the planted permutation, are interior, sorted,
+    one per row/column, and equal the oracle on one pair."""
+    hw_c = (64, 80)
+    N = hw_c[0] * hw_c[1]
+    B = 4
+    f0, f1, perm = synth.coarse_features(B, N, N, 256, 0.1, "planted", 1234)
+    d = run_coarse(f0, f1, (512, 640), hw_c, hw_c)
+    b, i, j = d["b_ids"].cpu(), d["i_ids"].cpu(), d["j_ids"].cpu()
+    assert b.numel() > B * 3500
+    assert torch.equal(perm[b, j], i)
+    inner = mo.interior_mask(64, 80, 2)
+    assert bool(inner[i].all()) and bool(inner[j].all())
+    key = (b * N + i) * N + j
+    assert bool((key[1:] > key[:-1]).all())
+    assert torch.unique(b * N + i).numel() == b.numel() and torch.unique(b * N + j).numel() == b.numel()
+    o = mo.coarse_match(f0[:1], f1[:1], (512, 640), hw_c, hw_c)
+    sel = b == 0
+    ours0 = {k: d[k].cpu()[sel] for k in ("b_ids", "i_ids", "j_ids", "mconf", "mkpts0_c", "mkpts1_c")}
+    o64 = mo.coarse_match(f0[:1], f1[:1], (512, 640), hw_c, hw_c, dtype=torch.float64, return_conf=True)
+    compare.check_coarse(ours0, o, o64["conf_matrix"])
+
+
+def test_coarse_rejects_bad_input():
+    m = coarse_module()
+    f = torch.zeros(1, 80, 256, dtype=torch.bfloat16)
+    with pytest.raises(_lib.FmError):
+        m(f, f, {"hw0_i": (64, 80), "hw0_c": (8, 10), "hw1_c": (8, 10)})   # CPU tensors
+    with pytest.raises(_lib.FmError):
+        m(f.to(DEV), f.to(DEV), {"hw0_i": (64, 80), "hw0_c": (8, 9), "hw1_c": (8, 10)})
+    m.train()
+    with pytest.raises(NotImplementedError):
+        m(f.to(DEV), f.to(DEV), {"hw0_i": (64, 80), "hw0_c": (8, 10), "hw1_c": (8, 10)})
+
+
+# ------------------------------------------------------------------------------ fine
+def fine_modules(p):
+    pre = modules.FinePreprocess(CFG).eval().to(DEV)
+    fin = modules.FineMatching(CFG["fine"]).eval().to(DEV)
+    with torch.no_grad():
+        pre.down_proj.weight.copy_(p["down_w"]); pre.down_proj.bias.copy_(p["down_b"])
+        pre.merge_feat.weight.copy_(p["merge_w"]); pre.merge_feat.bias.copy_(p["merge_b"])
+        fin.mix_feat_0.weight.copy_(p["mix_w0"].reshape(1, -1)); fin.mix_feat_0.bias.copy_(p["mix_b0"].reshape(1))
+        fin.mix_feat_1.weight.copy_(p["mix_w1"].reshape(1, -1)); fin.mix_feat_1.bias.copy_(p["mix_b1"].reshape(1))
+    return pre, fin
+
+
+@pytest.mark.parametrize("layout", ["nchw_f32", "nchw_bf16", "nhwc_bf16"])
+def test_fine_chain_golden(golden_dir, layout):
+    g = load(golden_dir, "fine_chain")
+    t = {k: torch.from_numpy(v) for k, v in g.items() if v.dtype != np.uint16}
+    fc0, fc1 = compare.from_bits(g["feat_c0"]), compare.from_bits(g["feat_c1"])
+    ff0, ff1 = compare.from_bits(g["feat_f0"]), compare.from_bits(g["feat_f1"])
+    if layout == "nchw_f32":
+        ff0, ff1 = ff0.float(), ff1.float()
+    elif layout == "nhwc_bf16":
+        ff0 = ff0.contiguous(memory_format=torch.channels_last)
+        ff1 = ff1.contiguous(memory_format=torch.channels_last)
+    hw_c, hw_f, hw_i = tuple(g["hw_c"]), tuple(g["hw_f"]), tuple(g["hw_i"])
+    pre, fin = fine_modules(t)
+    data = {"hw0_i": hw_i, "hw1_i": hw_i, "hw0_c": hw_c, "hw1_c": hw_c, "hw0_f": hw_f, "hw1_f": hw_f,
+            "b_ids": t["b_ids"].to(DEV), "i_ids": t["i_ids"].to(DEV), "j_ids": t["j_ids"].to(DEV),
+            "mkpts0_c": t["mkpts0_c"].to(DEV), "mkpts1_c": t["mkpts1_c"].to(DEV)}
+    w0, w1 = pre(ff0.to(DEV), ff1.to(DEV), fc0.to(DEV), fc1.to(DEV), data)
+    assert data["W"] == 7 and w0.dtype == torch.float32 and w0.shape == (40, 49, 64)
+    compare.check_windows(w0, g["win0"])
+    compare.check_windows(w1, g["win1"])
+    fin(w0, w1, data)
+    compare.check_fine(data["mkpts0_f"], data["mkpts1_f"], g["mkpts0_f"], g["mkpts1_f"])
+    # fine matching alone on the reference's own windows
+    fin(torch.from_numpy(g["win0"]).to(DEV), torch.from_numpy(g["win1"]).to(DEV), data)
+    compare.check_fine(data["mkpts0_f"], data["mkpts1_f"], g["mkpts0_f"], g["mkpts1_f"])
+    assert (data["mkpts0_f"].cpu() - t["mkpts0_f"]).abs().max() < 5e-5
+
+
+def test_fine_gather_without_merge(golden_dir):
+    g = load(golden_dir, "fine_chain")
+    t = {k: torch.from_numpy(v) for k, v in g.items() if v.dtype != np.uint16}
+    ff0, ff1 = compare.from_bits(g["feat_f0"]), compare.from_bits(g["feat_f1"])
+    hw_c, hw_f = tuple(g["hw_c"]), tuple(g["hw_f"])
+    cfg = dict(CFG, fine_concat_coarse_feat=False)
+    pre = modules.FinePreprocess(cfg).eval().to(DEV)
+    data = {"hw0_c": hw_c, "hw1_c": hw_c, "hw0_f": hw_f, "b_ids": t["b_ids"].to(DEV),
+            "i_ids": t["i_ids"].to(DEV), "j_ids": t["j_ids"].to(DEV)}
+    w0, w1 = pre(ff0.to(DEV), ff1.to(DEV), None, None, data)
+    r0, r1 = mo.fine_preprocess(ff0, ff1, None, None, t["b_ids"], t["i_ids"], t["j_ids"], hw_c, hw_c, hw_f, 7, None)
+    assert torch.equal(w0.cpu(), r0) and torch.equal(w1.cpu(), r1)   # a pure copy: bit-exact
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_fine_match_special(golden_dir, dtype):
+    g = load(golden_dir, "fine_match_special")
+    t = {k: torch.from_numpy(v) for k, v in g.items() if v.dtype != np.uint16}
+    w0, w1 = compare.from_bits(g["win0"]), compare.from_bits(g["win1"])
+    _, fin = fine_modules(dict(synth.hot_path_params(), **t))
+    data = {"hw0_i": tuple(g["hw_i"]), "hw0_f": tuple(g["hw_f"]),
+            "mkpts0_c": t["mkpts0_c"].to(DEV), "mkpts1_c": t["mkpts1_c"].to(DEV)}
+    fin(w0.to(DEV, dtype), w1.to(DEV, dtype), data)
+    compare.check_fine(data["mkpts0_f"], data["mkpts1_f"], g["mkpts0_f"], g["mkpts1_f"])
+    assert data["mkpts0_f"].shape == (24, 3)
+
+
+@pytest.mark.parametrize("M", [1, 7, 333, 5000])
+def test_fine_match_random_vs_oracle(M):
+    g = torch.Generator().manual_seed(M)
+    w0 = torch.randn(M, 49, 64, generator=g).bfloat16()
+    w1 = (w0.float() * 0.5 + torch.randn(M, 49, 64, generator=g)).bfloat16()
+    mk0 = torch.rand(M, 2, generator=g).mul(600).floor()
+    mk1 = torch.rand(M, 2, generator=g).mul(600).floor()
+    p = synth.hot_path_params(seed=M)
+    _, fin = fine_modules(p)
+    data = {"hw0_i": (512, 640), "hw0_f": (256, 320), "mkpts0_c": mk0.to(DEV), "mkpts1_c": mk1.to(DEV)}
+    fin(w0.to(DEV), w1.to(DEV), data)
+    r0, r1 = mo.fine_match(w0, w1, mk0, mk1, p, (512, 640), (256, 320))
+    compare.check_fine(data["mkpts0_f"], data["mkpts1_f"], r0, r1)
+
+
+def test_empty_match_list(golden_dir):
+    """M == 0: same keys, shapes and dtypes as the reference (fine_preprocess.py:37-40,
+    fine_matching_new.py:40-48)."""
+    g = load(golden_dir, "coarse_iid")
+    f0, f1 = compare.from_bits(g["feat_c0"]), compare.from_bits(g["feat_c1"])
+    hw_i, hw_c = tuple(g["hw_i"]), tuple(g["hw0_c"])
+    d = run_coarse(f0, f1, hw_i, hw_c, hw_c)
+    assert d["b_ids"].shape == (0,) and d["mkpts0_c"].shape == (0, 2) and d["mconf"].shape == (0,)
+    d["hw0_f"] = (hw_c[0] * 4, hw_c[1] * 4)
+    pre, fin = fine_modules(synth.hot_path_params())
+    ff = torch.zeros(1, 64, hw_c[0] * 4, hw_c[1] * 4, device=DEV)
+    w0, w1 = pre(ff, ff, f0.to(DEV), f1.to(DEV), d)
+    assert w0.shape == (0, 49, 64) and w1.shape == (0, 49, 64)
+    fin(w0, w1, d)
+    assert d["expec_f"].shape == (0, 3) and d["mkpts0_f"].shape == (0, 2)
+
+
+# ------------------------------------------------------------------------------ whole head
+def test_match_head_end_to_end_vs_oracle():
+    """coarse -> gather -> fine match on one planted 320x320-shaped pair batch."""
+    hw_c, hw_f, hw_i = (40, 40), (160, 160), (320, 320)
+    N = 1600
+    B = 2
+    fc0, fc1, _ = synth.coarse_features(B, N, N, 256, 0.1, "planted", 3)
+    ff0, ff1 = synth.fine_features(B, 64, 160, 160, 8)
+    p = synth.hot_path_params(seed=4)
+    pre, fin = fine_modules(p)
+    cm = coarse_module()
+    data = {"hw0_i": hw_i, "hw1_i": hw_i, "hw0_c": hw_c, "hw1_c": hw_c, "hw0_f": hw_f, "hw1_f": hw_f}
+    cm(fc0.to(DEV), fc1.to(DEV), data)
+    w0, w1 = pre(ff0.to(DEV), ff1.to(DEV), fc0.to(DEV), fc1.to(DEV), data)
+    fin(w0, w1, data)
+    ref = mo.match_head(fc0, fc1, ff0, ff1, hw_i, hw_c, hw_c, hw_f, CFG["match_coarse"], p, p)
+    o64 = mo.coarse_match(fc0, fc1, hw_i, hw_c, hw_c, dtype=torch.float64, return_conf=True)
+    assert compare.check_coarse(data, ref, o64["conf_matrix"]) == 0
+    assert data["b_ids"].numel() > 2000
+    compare.check_fine(data["mkpts0_f"], data["mkpts1_f"], ref["mkpts0_f"], ref["mkpts1_f"])
