@@ -34,7 +34,8 @@ namespace fm {
 
 namespace {
 
-struct __align__(8) SmemCtl {
+struct __align__(16) SmemCtl {
+    float colscratch[kEpiWarps][128];   // first: float4 stores need 16-byte alignment
     uint64_t a_full[kAStages];
     uint64_t a_empty[kAStages];
     uint64_t b_full;
@@ -43,7 +44,6 @@ struct __align__(8) SmemCtl {
     uint64_t t_empty[2];
     uint32_t tmem_base;
     int cand_count;
-    float colscratch[kEpiWarps][128];
 };
 
 constexpr size_t kSmemOperands = static_cast<size_t>(kBChunkBytes) * (kMaxC / kChunkK) +
