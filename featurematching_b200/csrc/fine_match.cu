@@ -207,7 +207,50 @@ cudaError_t launch(const void* win0, const void* win1, const float* mk0, const f
     return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------- match records for the gather
+struct __align__(8) MatchRecord {
+    int pair, i, j;
+    float conf, x0, y0, std0, x1, y1, std1;
+};
+static_assert(sizeof(MatchRecord) == FM_RECORD_BYTES, "record layout");
+
+__global__ void __launch_bounds__(256) pack_matches_kernel(const int64_t* __restrict__ b_ids,
+                                                           const int64_t* __restrict__ i_ids,
+                                                           const int64_t* __restrict__ j_ids,
+                                                           const float* __restrict__ mconf,
+                                                           const float* __restrict__ mk0,
+                                                           const float* __restrict__ mk1,
+                                                           const int* __restrict__ count, int capacity,
+                                                           int pair_offset, MatchRecord* __restrict__ rec) {
+    const int M = min(*count, capacity);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        MatchRecord h = {M, pair_offset, 0, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        rec[0] = h;
+    }
+    for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < M; m += gridDim.x * blockDim.x) {
+        MatchRecord r;
+        r.pair = static_cast<int>(b_ids[m]) + pair_offset;
+        r.i = static_cast<int>(i_ids[m]);
+        r.j = static_cast<int>(j_ids[m]);
+        r.conf = mconf[m];
+        r.x0 = mk0[3 * m]; r.y0 = mk0[3 * m + 1]; r.std0 = mk0[3 * m + 2];
+        r.x1 = mk1[3 * m]; r.y1 = mk1[3 * m + 1]; r.std1 = mk1[3 * m + 2];
+        rec[1 + m] = r;
+    }
+}
+
 }  // namespace
+
+cudaError_t launch_pack_matches(const int64_t* b_ids, const int64_t* i_ids, const int64_t* j_ids, const float* mconf,
+                                const float* mk0, const float* mk1, const int* count, int capacity, int pair_offset,
+                                void* records, int num_sms, cudaStream_t st) {
+    int grid = (capacity + 255) / 256;
+    if (grid > num_sms * 8) grid = num_sms * 8;
+    if (grid < 1) grid = 1;
+    pack_matches_kernel<<<grid, 256, 0, st>>>(b_ids, i_ids, j_ids, mconf, mk0, mk1, count, capacity, pair_offset,
+                                              static_cast<MatchRecord*>(records));
+    return cudaGetLastError();
+}
 
 cudaError_t launch_fine_match(const void* win0, const void* win1, int dtype, const float* mk0, const float* mk1,
                               const float* w0, const float* b0, const float* w1, const float* b1, const int* count,

@@ -3,6 +3,8 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
+#include <vector>
 
 #include "fm_common.cuh"
 
@@ -20,6 +22,31 @@ void set_error(const char* fmt, ...) {
 static int cuda_fail(cudaError_t e, const char* what) {
     set_error("%s: %s", what, cudaGetErrorString(e));
     return FM_ERR_CUDA;
+}
+
+// ---------------------------------------------------------------- stage timers (fm_profile_*)
+struct StageTimers {
+    std::mutex mu;
+    bool on = false;
+    std::vector<cudaEvent_t> pool;   // pairs: [2k] start, [2k + 1] stop
+    size_t used = 0;                 // events handed out since the last collect
+};
+static StageTimers g_timers;
+constexpr size_t kMaxTimedCalls = 4096;
+
+// Hands out the next (start, stop) pair, or false when disabled / full.
+static bool timer_pair(cudaEvent_t* a, cudaEvent_t* b) {
+    std::lock_guard<std::mutex> lk(g_timers.mu);
+    if (!g_timers.on || g_timers.used >= 2 * kMaxTimedCalls) return false;
+    while (g_timers.pool.size() < g_timers.used + 2) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return false;
+        g_timers.pool.push_back(e);
+    }
+    *a = g_timers.pool[g_timers.used];
+    *b = g_timers.pool[g_timers.used + 1];
+    g_timers.used += 2;
+    return true;
 }
 
 static int sm_count() {
@@ -125,6 +152,9 @@ cudaError_t launch_fine_gather(const void* ff0, const void* ff1, const void* fc0
                                const float* merge_w, const float* merge_b, void* win0, void* win1, int out_dtype,
                                int num_sms, cudaStream_t st);
 cudaError_t launch_to_nhwc(const void* src, int src_dtype, int B, int C, int H, int W, void* dst, cudaStream_t st);
+cudaError_t launch_pack_matches(const int64_t* b_ids, const int64_t* i_ids, const int64_t* j_ids, const float* mconf,
+                                const float* mk0, const float* mk1, const int* count, int capacity, int pair_offset,
+                                void* records, int num_sms, cudaStream_t st);
 cudaError_t launch_fine_match(const void* win0, const void* win1, int dtype, const float* mk0, const float* mk1,
                               const float* w0, const float* b0, const float* w1, const float* b1, const int* count,
                               int capacity, int WW, float scale, float* out0, float* out1, int num_sms,
@@ -191,7 +221,11 @@ static int coarse_match_impl(bool simt, const void* feat_c0, const void* feat_c1
     sp.cand_thr = kCandMargin * thr;
     sp.norm0 = w.norm0; sp.maxnorm = w.maxnorm; sp.rowpart = w.rowpart; sp.colpart = w.colpart;
     sp.cand = w.cand; sp.unit_count = w.unit_count; sp.status = status;
+    cudaEvent_t ev0, ev1;
+    const bool timed = !simt && timer_pair(&ev0, &ev1);
+    if (timed) cudaEventRecord(ev0, st);
     e = simt ? launch_coarse_stats_simt(f0, f1, sp, st) : launch_coarse_stats_tc(f0, f1, sp, sms, st);
+    if (timed) cudaEventRecord(ev1, st);
     if (e != cudaSuccess) return cuda_fail(e, simt ? "coarse_stats_simt launch" : "coarse_stats_tc launch");
 
     CoarseResolveParams rp{};
@@ -354,6 +388,47 @@ int fm_fine_match(const void* win0, const void* win1, int win_dtype, const float
     cudaError_t e = launch_fine_match(win0, win1, win_dtype, mkpts0_c, mkpts1_c, mix_w0, mix_b0, mix_w1, mix_b1, count,
                                       capacity, WW, scale, mkpts0_f, mkpts1_f, sms, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return cuda_fail(e, "fine_match launch");
+    return FM_OK;
+}
+
+int fm_pack_matches(const int64_t* b_ids, const int64_t* i_ids, const int64_t* j_ids, const float* mconf,
+                    const float* mkpts0_f, const float* mkpts1_f, const int32_t* count, int capacity, int pair_offset,
+                    void* records, void* stream) {
+    if (!b_ids || !i_ids || !j_ids || !mconf || !mkpts0_f || !mkpts1_f || !count || !records || capacity < 0) {
+        set_error("bad argument to fm_pack_matches");
+        return FM_ERR_BAD_ARG;
+    }
+    const int sms = sm_count();
+    if (sms <= 0) { set_error("no CUDA device available (this library has no CPU path)"); return FM_ERR_CUDA; }
+    cudaError_t e = launch_pack_matches(b_ids, i_ids, j_ids, mconf, mkpts0_f, mkpts1_f, count, capacity, pair_offset,
+                                        records, sms, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "pack_matches launch");
+    return FM_OK;
+}
+
+int fm_profile_enable(int on) {
+    std::lock_guard<std::mutex> lk(g_timers.mu);
+    g_timers.on = on != 0;
+    if (!on) g_timers.used = 0;
+    return FM_OK;
+}
+
+int fm_profile_collect(float* ms_sum, int* launches) {
+    if (!ms_sum || !launches) { set_error("null pointer argument"); return FM_ERR_BAD_ARG; }
+    std::lock_guard<std::mutex> lk(g_timers.mu);
+    float total = 0.f;
+    int n = 0;
+    for (size_t k = 0; k + 1 < g_timers.used; k += 2) {
+        cudaError_t e = cudaEventSynchronize(g_timers.pool[k + 1]);
+        float ms = 0.f;
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, g_timers.pool[k], g_timers.pool[k + 1]);
+        if (e != cudaSuccess) { g_timers.used = 0; return cuda_fail(e, "fm_profile_collect"); }
+        total += ms;
+        ++n;
+    }
+    g_timers.used = 0;
+    *ms_sum = total;
+    *launches = n;
     return FM_OK;
 }
 

@@ -1,0 +1,187 @@
+"""Sync-free matching head for a batch of frame pairs, and the cross-GPU match-list gather.
+
+`MatchHead` chains the three drop-in modules of modules.py the way network/net.py:75-83 does
+(coarse match -> window gather -> [fine transformer, out of scope, optional callable] -> fine
+match), but keeps the match count on the device: every buffer is sized for `capacity` matches
+and the kernels read the count from the coarse status word, so a batch costs one host
+synchronisation (at the caller's choosing) instead of the reference's one per stage
+(torch.where at coarse_matching_new.py:109, the shape test at fine_preprocess.py:37).
+
+`gather_matches` is the one cross-GPU step: ranks own disjoint frame pairs; their packed match
+records are exchanged with a single padded all_gather (NCCL over NVLink on GPUs, gloo in the CPU
+tests) -- the analogue of the reference's pickled all_gather (utils/comm.py:141-176).
+"""
+import numpy as np
+import torch
+
+from . import _lib, modules
+
+RECORD_DTYPE = np.dtype([("pair", "<i4"), ("i", "<i4"), ("j", "<i4"), ("conf", "<f4"),
+                         ("x0", "<f4"), ("y0", "<f4"), ("std0", "<f4"),
+                         ("x1", "<f4"), ("y1", "<f4"), ("std1", "<f4")])
+assert RECORD_DTYPE.itemsize == _lib.RECORD_BYTES
+
+
+class HeadResult:
+    """Device-side outputs of one MatchHead.run call (padded to `capacity`)."""
+    __slots__ = ("coarse", "win0", "win1", "mkpts0_f", "mkpts1_f", "records", "capacity")
+
+    @property
+    def count(self):
+        return self.coarse.status[_lib.ST_COUNT:_lib.ST_COUNT + 1]
+
+
+class MatchHead:
+    def __init__(self, config, device, window_dtype=torch.float32, fine_transformer=None):
+        self.device = torch.device(device)
+        self.coarse_matching = modules.CoarseMatching(config['match_coarse']).eval()
+        self.fine_preprocess = modules.FinePreprocess(config).eval().to(self.device)
+        self.fine_preprocess.out_dtype = window_dtype
+        self.fine_matching = modules.FineMatching(config['fine']).eval().to(self.device)
+        self.fine_transformer = fine_transformer
+        self._res = None
+        self._host = {}
+
+    def load_params(self, p):
+        """p: dict with down_w/down_b/merge_w/merge_b/mix_w0/mix_b0/mix_w1/mix_b1 (synth.hot_path_params)."""
+        with torch.no_grad():
+            pre, fin = self.fine_preprocess, self.fine_matching
+            if pre.cat_c_feat:
+                pre.down_proj.weight.copy_(p["down_w"]); pre.down_proj.bias.copy_(p["down_b"])
+                pre.merge_feat.weight.copy_(p["merge_w"]); pre.merge_feat.bias.copy_(p["merge_b"])
+            fin.mix_feat_0.weight.copy_(p["mix_w0"].reshape(1, -1)); fin.mix_feat_0.bias.copy_(p["mix_b0"].reshape(1))
+            fin.mix_feat_1.weight.copy_(p["mix_w1"].reshape(1, -1)); fin.mix_feat_1.bias.copy_(p["mix_b1"].reshape(1))
+        self._params = None
+
+    @staticmethod
+    def default_capacity(B, hw0_c, hw1_c, border_rm):
+        """Mutual nearest neighbours of interior cells: at most one per interior cell of the
+        smaller grid (exact ties aside, which the status flags report)."""
+        n0 = max(hw0_c[0] - 2 * border_rm, 0) * max(hw0_c[1] - 2 * border_rm, 0)
+        n1 = max(hw1_c[0] - 2 * border_rm, 0) * max(hw1_c[1] - 2 * border_rm, 0)
+        return max(B * min(n0, n1), 1)
+
+    def _buffers(self, capacity, WW, Cf):
+        r = self._res
+        if r is not None and r.capacity >= capacity:
+            return r
+        dev = self.device
+        r = HeadResult()
+        r.capacity = capacity
+        r.coarse = None
+        wd = self.fine_preprocess.out_dtype
+        r.win0 = torch.empty(capacity, WW, Cf, dtype=wd, device=dev)
+        r.win1 = torch.empty(capacity, WW, Cf, dtype=wd, device=dev)
+        r.mkpts0_f = torch.empty(capacity, 3, dtype=torch.float32, device=dev)
+        r.mkpts1_f = torch.empty(capacity, 3, dtype=torch.float32, device=dev)
+        r.records = torch.empty((capacity + 1) * _lib.RECORD_BYTES, dtype=torch.uint8, device=dev)
+        self._res = r
+        return r
+
+    def run(self, feat_c0, feat_c1, feat_f0, feat_f1, hw0_i, hw0_c, hw1_c, hw0_f, capacity=None,
+            pair_offset=0, pack=True):
+        """Enqueues the whole head on the current stream; no host synchronisation.
+        feat_c*: [B, N, C] bf16/fp32; feat_f*: [B, Cf, Hf, Wf] (channels-last bf16 is read in place)."""
+        B = feat_c0.shape[0]
+        cm, pre, fin = self.coarse_matching, self.fine_preprocess, self.fine_matching
+        if capacity is None:
+            capacity = self.default_capacity(B, hw0_c, hw1_c, cm.border_rm)
+        WW, Cf = pre.W * pre.W, feat_f0.shape[1]
+        r = self._buffers(capacity, WW, Cf)
+        with torch.no_grad():
+            r.coarse = cm.match_raw(feat_c0, feat_c1, hw0_i, hw0_c, hw1_c, capacity=r.capacity, out=r.coarse)
+            c = r.coarse
+            count = c.status   # status[0] = match count
+            pre.gather(feat_f0, feat_f1, feat_c0, feat_c1, c.b_ids, c.i_ids, c.j_ids, hw0_c, hw1_c,
+                       hw0_f, count=count, capacity=r.capacity, out=(r.win0, r.win1))
+            w0, w1 = r.win0, r.win1
+            if self.fine_transformer is not None:
+                # out-of-scope PyTorch module (network/net.py:79-80); needs exact-length inputs
+                M = int(count[0].item())
+                w0, w1 = self.fine_transformer(r.win0[:M], r.win1[:M])
+            scale = float(hw0_i[0]) / float(hw0_f[0])
+            fin.refine(w0, w1, c.mkpts0_c, c.mkpts1_c, scale, count=count,
+                       out=(r.mkpts0_f, r.mkpts1_f))
+            if pack:
+                lib = _lib.load()
+                with torch.cuda.device(self.device):
+                    rc = lib.fm_pack_matches(_lib.ptr(c.b_ids), _lib.ptr(c.i_ids), _lib.ptr(c.j_ids),
+                                             _lib.ptr(c.mconf), _lib.ptr(r.mkpts0_f), _lib.ptr(r.mkpts1_f),
+                                             _lib.ptr(count), r.capacity, int(pair_offset),
+                                             _lib.ptr(r.records), _lib.stream_ptr(self.device))
+                _lib.check(rc, "fm_pack_matches")
+        return r
+
+    def check_status(self, r):
+        """One small synchronising copy; raises on device-reported overflow / range loss."""
+        st = self.coarse_matching.read_status(r.coarse)
+        flags = st[_lib.ST_FLAGS]
+        if flags:
+            raise _lib.FmError(f"coarse status flags {flags:#x} (cand overflow=1, output overflow=2, "
+                               f"tie overflow=4, range=8); status={st}")
+        return st[_lib.ST_COUNT]
+
+    # ---------------------------------------------------------------- host-buffer entry point
+    def _staging(self, name, t):
+        buf = self._host.get(name)
+        if buf is None or buf.shape != t.shape or buf.dtype != t.dtype:
+            buf = torch.empty_like(t, device=self.device)   # keeps the strides (channels-last maps)
+            self._host[name] = buf
+        return buf
+
+    def match_host(self, feat_c0, feat_c1, feat_f0, feat_f1, hw0_i, hw0_c, hw1_c, hw0_f, pair_offset=0):
+        """End-to-end call on HOST tensors (pinned for full copy bandwidth): copies the features
+        to the device, runs the head, and returns the match records as a numpy structured array
+        (RECORD_DTYPE).  Also returns the bytes moved each way."""
+        dev_in = []
+        h2d = 0
+        for name, t in (("c0", feat_c0), ("c1", feat_c1), ("f0", feat_f0), ("f1", feat_f1)):
+            d = self._staging(name, t)
+            d.copy_(t, non_blocking=True)
+            h2d += t.numel() * t.element_size()
+            dev_in.append(d)
+        r = self.run(*dev_in, hw0_i, hw0_c, hw1_c, hw0_f, pair_offset=pair_offset)
+        M = self.check_status(r)
+        nbytes = (M + 1) * _lib.RECORD_BYTES
+        out = self._host.get("rec")
+        if out is None or out.numel() < nbytes:
+            out = torch.empty(max(nbytes, (r.capacity + 1) * _lib.RECORD_BYTES), dtype=torch.uint8).pin_memory()
+            self._host["rec"] = out
+        out[:nbytes].copy_(r.records[:nbytes], non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        rec = out[:nbytes].numpy().view(RECORD_DTYPE)
+        return rec[1:], h2d, nbytes + _lib.STATUS_WORDS * 4
+
+
+def unpack_records(buf, capacity, world):
+    """[world * (capacity + 1) * 40] uint8 (host) -> list of per-rank structured arrays."""
+    a = buf.numpy().view(RECORD_DTYPE).reshape(world, capacity + 1)
+    return [a[r, 1:1 + int(a[r, 0]["pair"])] for r in range(world)]
+
+
+def gather_matches(records, capacity, group=None):
+    """All ranks receive every rank's packed records: one padded all_gather, no size exchange and
+    no host synchronisation (the count travels in each rank's header record).  Every rank must
+    call it, also with zero matches.  `records`: uint8 [(capacity + 1) * 40] on the rank's device
+    (CPU tensors with the gloo backend).  Returns uint8 [world * (capacity + 1) * 40]."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    n = (capacity + 1) * _lib.RECORD_BYTES
+    out = torch.empty(world * n, dtype=torch.uint8, device=records.device)
+    dist.all_gather_into_tensor(out, records[:n].contiguous(), group=group)
+    return out
+
+
+def shard_pairs(num_pairs, rank, world):
+    """Contiguous block partition of frame pairs over ranks: [begin, end)."""
+    base, rem = divmod(num_pairs, world)
+    begin = rank * base + min(rank, rem)
+    return begin, begin + base + (1 if rank < rem else 0)
+
+
+def shard_sequence(num_frames, rank, world):
+    """Consecutive-frame matching of a sequence (pairs (k, k + 1), the pattern of
+    datasets/scared_new2.py:76-83): rank owns pairs [begin, end) and therefore frames
+    [begin, end] -- a one-frame halo, so no pair straddles two ranks."""
+    begin, end = shard_pairs(max(num_frames - 1, 0), rank, world)
+    return begin, end, (begin, end + 1 if end > begin else begin)

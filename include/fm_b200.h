@@ -141,6 +141,18 @@ FM_API int fm_fine_match(const void* win0, const void* win1, int win_dtype, cons
                   const float* mix_w1, const float* mix_b1, const int32_t* count, int capacity,
                   int WW, int Cf, float scale, float* mkpts0_f, float* mkpts1_f, void* stream);
 
+/* ---------------------------------------------------------------- match records
+ * Packs the match list into 40-byte records for the cross-GPU gather (the analogue of the
+ * reference's pickled all_gather, utils/comm.py:141-176, used at lightning_new.py:291-295):
+ *   record = { int32 pair, int32 i, int32 j, float conf, float x0, y0, std0, x1, y1, std1 }
+ * records[0] is a header { int32 count, int32 pair_offset, 0... }; match m goes to records[1 + m]
+ * with pair = b_ids[m] + pair_offset.  records: (capacity + 1) * 40 bytes. */
+#define FM_RECORD_BYTES 40
+FM_API int fm_pack_matches(const int64_t* b_ids, const int64_t* i_ids, const int64_t* j_ids,
+                           const float* mconf, const float* mkpts0_f, const float* mkpts1_f,
+                           const int32_t* count, int capacity, int pair_offset, void* records,
+                           void* stream);
+
 /* ---------------------------------------------------------------- test / profiling hooks
  * Same contract as fm_coarse_match, but the score statistics come from a plain SIMT kernel
  * instead of the tcgen05 kernel.  Exists so tests can tell a tensor-core plumbing bug from a
@@ -163,6 +175,13 @@ FM_API int fm_debug_coarse_lse(const void* workspace, int B, int N0, int N1, int
 FM_API int fm_profile_coarse_stats(const void* feat_c0, const void* feat_c1, int B, int N0, int N1, int C,
                             float temperature, float thr, void* workspace, size_t workspace_bytes,
                             int cand_per_row, int iters, float* ms, void* stream);
+
+/* Stage timers.  While enabled, every fm_coarse_match call brackets its statistics kernel (the
+ * tcgen05 GEMM + fused dual-softmax sums) with a pair of CUDA events on the call's stream (up to
+ * 4096 calls are kept).  fm_profile_collect synchronises on the recorded events, returns the
+ * summed milliseconds and the number of launches, and clears the list. */
+FM_API int fm_profile_enable(int on);
+FM_API int fm_profile_collect(float* ms_sum, int* launches);
 
 #ifdef __cplusplus
 }
