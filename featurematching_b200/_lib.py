@@ -33,8 +33,9 @@ SIGNATURES = {
     "fm_profile_coarse_stats": (_I, [_P, _P, _I, _I, _I, _I, _F, _F, _P, _Z, _I, _I,
                                      _c.POINTER(_c.c_float), _P]),
     "fm_fine_to_nhwc_bf16": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),
+    "fm_fine_gather_workspace_bytes": (_Z, [_I] * 6),
     "fm_fine_gather": (_I, [_P, _P, _P, _P, _I, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I,
-                            _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P]),
+                            _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P, _Z, _P]),
     "fm_pack_matches": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P]),
     "fm_profile_enable": (_I, [_I]),
     "fm_profile_collect": (_I, [_c.POINTER(_c.c_float), _c.POINTER(_c.c_int)]),

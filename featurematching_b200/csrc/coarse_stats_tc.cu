@@ -29,6 +29,7 @@
 
 #include "fm_common.cuh"
 #include "fm_ptx.cuh"
+#include "fm_tmap.cuh"
 
 namespace fm {
 
@@ -312,40 +313,41 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
     if (warp == 2) tmem_dealloc<512>(tmem_base);
 }
 
-// ---------------------------------------------------------------- host: tensor maps + launch
+// [B, N, C] bf16 row-major viewed as a 3-D tensor (C, N, B); box = 64 channels x `rows` tokens,
+// 128-byte swizzle; rows past N are zero-filled and never bleed into the next pair.
+bool make_feature_map(CUtensorMap* m, const __nv_bfloat16* ptr, int B, int N, int C, int rows) {
+    const uint64_t dims[3] = {static_cast<uint64_t>(C), static_cast<uint64_t>(N), static_cast<uint64_t>(B)};
+    const uint64_t strides[2] = {static_cast<uint64_t>(C) * 2, static_cast<uint64_t>(N) * C * 2};
+    const uint32_t box[3] = {static_cast<uint32_t>(kChunkK), static_cast<uint32_t>(rows), 1};
+    return encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, ptr, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- host: tensor maps
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
                                   CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
                                   CUtensorMapFloatOOBfill);
 
-EncodeTiledFn get_encode_fn() {
+bool encode_tiled(CUtensorMap* m, CUtensorMapDataType dt, int rank, const void* ptr, const uint64_t* dims,
+                  const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swizzle) {
     static EncodeTiledFn fn = nullptr;
-    if (fn) return fn;
-    void* sym = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) != cudaSuccess ||
-        qres != cudaDriverEntryPointSuccess)
-        return nullptr;
-    fn = reinterpret_cast<EncodeTiledFn>(sym);
-    return fn;
+    if (!fn) {
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) != cudaSuccess ||
+            qres != cudaDriverEntryPointSuccess)
+            return false;
+        fn = reinterpret_cast<EncodeTiledFn>(sym);
+    }
+    cuuint64_t d[5], st[4];
+    cuuint32_t bx[5], es[5];
+    for (int k = 0; k < rank; ++k) { d[k] = dims[k]; bx[k] = box[k]; es[k] = 1; }
+    for (int k = 0; k + 1 < rank; ++k) st[k] = strides_bytes[k];
+    return fn(m, dt, static_cast<cuuint32_t>(rank), const_cast<void*>(ptr), d, st, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
-
-// [B, N, C] bf16 row-major viewed as a 3-D tensor (C, N, B); box = 64 channels x `rows` tokens,
-// 128-byte swizzle; rows past N are zero-filled and never bleed into the next pair.
-bool make_feature_map(CUtensorMap* m, const __nv_bfloat16* ptr, int B, int N, int C, int rows) {
-    EncodeTiledFn enc = get_encode_fn();
-    if (!enc) return false;
-    cuuint64_t dims[3] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(N), static_cast<cuuint64_t>(B)};
-    cuuint64_t strides[2] = {static_cast<cuuint64_t>(C) * 2, static_cast<cuuint64_t>(N) * C * 2};
-    cuuint32_t box[3] = {static_cast<cuuint32_t>(kChunkK), static_cast<cuuint32_t>(rows), 1};
-    cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<__nv_bfloat16*>(ptr), dims, strides,
-                     box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    return r == CUDA_SUCCESS;
-}
-
-}  // namespace
 
 cudaError_t launch_coarse_stats_tc(const __nv_bfloat16* f0, const __nv_bfloat16* f1,
                                    const CoarseStatsParams& p, int num_sms, cudaStream_t st) {

@@ -151,6 +151,14 @@ cudaError_t launch_fine_gather(const void* ff0, const void* ff1, const void* fc0
                                int stride, int pad, int W, const float* down_w, const float* down_b,
                                const float* merge_w, const float* merge_b, void* win0, void* win1, int out_dtype,
                                int num_sms, cudaStream_t st);
+bool fine_gather_tc_supported(int Cf, int Cc, int W);
+size_t fine_gather_tc_workspace_bytes(int B, int N0, int N1, int Cc, bool f32_tokens);
+cudaError_t launch_fine_gather_tc(const void* ff0, const void* ff1, const void* fc0, const void* fc1, int featc_dtype,
+                                  const int64_t* b_ids, const int64_t* i_ids, const int64_t* j_ids, const int* count,
+                                  int capacity, int B, int Hf, int Wf, int N0, int N1, int Cc, int w0c, int w1c,
+                                  int stride, int pad, int W, const float* down_w, const float* down_b,
+                                  const float* merge_w, const float* merge_b, void* win0, void* win1, int out_dtype,
+                                  void* workspace, size_t workspace_bytes, int num_sms, cudaStream_t st);
 cudaError_t launch_to_nhwc(const void* src, int src_dtype, int B, int C, int H, int W, void* dst, cudaStream_t st);
 cudaError_t launch_pack_matches(const int64_t* b_ids, const int64_t* i_ids, const int64_t* j_ids, const float* mconf,
                                 const float* mk0, const float* mk1, const int* count, int capacity, int pair_offset,
@@ -346,11 +354,17 @@ int fm_fine_to_nhwc_bf16(const void* src, int src_dtype, int B, int C, int H, in
     return FM_OK;
 }
 
+size_t fm_fine_gather_workspace_bytes(int B, int N0, int N1, int Cc, int Cf, int featc_dtype) {
+    if (B < 1 || N0 < 1 || N1 < 1 || Cc < 1 || !dtype_ok(featc_dtype)) return 0;
+    if (!fine_gather_tc_supported(Cf, Cc, 7)) return 0;   // the SIMT path needs no workspace
+    return fine_gather_tc_workspace_bytes(B, N0, N1, Cc, featc_dtype == FM_DTYPE_F32);
+}
+
 int fm_fine_gather(const void* feat_f0, const void* feat_f1, const void* feat_c0, const void* feat_c1, int featc_dtype,
                    const int64_t* b_ids, const int64_t* i_ids, const int64_t* j_ids, const int32_t* count, int capacity,
                    int B, int Hf, int Wf, int Cf, int N0, int N1, int Cc, int w0c, int w1c, int stride, int pad, int W,
                    const float* down_w, const float* down_b, const float* merge_w, const float* merge_b, void* win0,
-                   void* win1, int out_dtype, void* stream) {
+                   void* win1, int out_dtype, void* workspace, size_t workspace_bytes, void* stream) {
     if (!feat_f0 || !feat_f1 || !b_ids || !i_ids || !j_ids || !win0 || !win1) { set_error("null pointer argument"); return FM_ERR_BAD_ARG; }
     if (Cf != 64) { set_error("Cf = %d unsupported (fine descriptors have 64 channels)", Cf); return FM_ERR_UNSUPPORTED; }
     if (W < 2 || W * W > 64) { set_error("window %d unsupported (need 2 <= W and W*W <= 64)", W); return FM_ERR_UNSUPPORTED; }
@@ -362,9 +376,28 @@ int fm_fine_gather(const void* feat_f0, const void* feat_f1, const void* feat_c0
     if (capacity == 0) return FM_OK;
     const int sms = sm_count();
     if (sms <= 0) { set_error("no CUDA device available (this library has no CPU path)"); return FM_ERR_CUDA; }
-    cudaError_t e = launch_fine_gather(feat_f0, feat_f1, feat_c0, feat_c1, featc_dtype, b_ids, i_ids, j_ids, count,
-                                       capacity, B, Hf, Wf, N0, N1, Cc, w0c, w1c, stride, pad, W, down_w, down_b,
-                                       merge_w, merge_b, win0, win1, out_dtype, sms, static_cast<cudaStream_t>(stream));
+    cudaError_t e;
+    if (merge && fine_gather_tc_supported(Cf, Cc, W)) {
+        if (N0 < 1 || N1 < 1) { set_error("N0, N1 must be >= 1"); return FM_ERR_BAD_ARG; }
+        if ((reinterpret_cast<uintptr_t>(feat_f0) | reinterpret_cast<uintptr_t>(feat_f1) | reinterpret_cast<uintptr_t>(feat_c0) |
+             reinterpret_cast<uintptr_t>(feat_c1) | reinterpret_cast<uintptr_t>(win0) | reinterpret_cast<uintptr_t>(win1) |
+             reinterpret_cast<uintptr_t>(workspace)) & 15) {
+            set_error("feature, window and workspace pointers must be 16-byte aligned");
+            return FM_ERR_BAD_ARG;
+        }
+        const size_t need = fine_gather_tc_workspace_bytes(B, N0, N1, Cc, featc_dtype == FM_DTYPE_F32);
+        if (!workspace || workspace_bytes < need) {
+            set_error("fine gather workspace too small: need %zu bytes, got %zu", need, workspace ? workspace_bytes : 0);
+            return FM_ERR_WORKSPACE;
+        }
+        e = launch_fine_gather_tc(feat_f0, feat_f1, feat_c0, feat_c1, featc_dtype, b_ids, i_ids, j_ids, count, capacity, B,
+                                  Hf, Wf, N0, N1, Cc, w0c, w1c, stride, pad, W, down_w, down_b, merge_w, merge_b, win0,
+                                  win1, out_dtype, workspace, workspace_bytes, sms, static_cast<cudaStream_t>(stream));
+    } else {
+        e = launch_fine_gather(feat_f0, feat_f1, feat_c0, feat_c1, featc_dtype, b_ids, i_ids, j_ids, count, capacity, B,
+                               Hf, Wf, N0, N1, Cc, w0c, w1c, stride, pad, W, down_w, down_b, merge_w, merge_b, win0,
+                               win1, out_dtype, sms, static_cast<cudaStream_t>(stream));
+    }
     if (e != cudaSuccess) return cuda_fail(e, "fine_gather launch");
     return FM_OK;
 }

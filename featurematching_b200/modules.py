@@ -193,6 +193,7 @@ class FinePreprocess(nn.Module):
             self.down_proj = nn.Linear(d_model_c, d_model_f, bias=True)
             self.merge_feat = nn.Linear(2 * d_model_f, d_model_f, bias=True)
         self.out_dtype = torch.float32   # the reference hands fp32 windows to the fine transformer
+        self._ws = _Workspace()
         self._reset_parameters()
 
     def _reset_parameters(self):   # fine_preprocess.py:27-30
@@ -250,6 +251,8 @@ class FinePreprocess(nn.Module):
             params = [None] * 4
             cdt = _lib.DTYPE_BF16
         ids = [t.to(device=dev, dtype=torch.int64).contiguous() for t in (b_ids, i_ids, j_ids)]
+        nbytes = lib.fm_fine_gather_workspace_bytes(B, N0, N1, Cc, Cf, cdt) if self.cat_c_feat else 0
+        ws = self._ws.get(nbytes, dev) if nbytes else None
         with torch.cuda.device(dev):
             rc = lib.fm_fine_gather(_lib.ptr(nh0), _lib.ptr(nh1), _lib.ptr(c0), _lib.ptr(c1), cdt,
                                     _lib.ptr(ids[0]), _lib.ptr(ids[1]), _lib.ptr(ids[2]),
@@ -257,7 +260,7 @@ class FinePreprocess(nn.Module):
                                     int(hw0_c[1]), int(hw1_c[1]), stride, 2, W,
                                     _lib.ptr(params[0]), _lib.ptr(params[1]), _lib.ptr(params[2]),
                                     _lib.ptr(params[3]), _lib.ptr(win0), _lib.ptr(win1),
-                                    _lib.dtype_code(win0), _lib.stream_ptr(dev))
+                                    _lib.dtype_code(win0), _lib.ptr(ws), nbytes, _lib.stream_ptr(dev))
         _lib.check(rc, "fm_fine_gather")
         return win0, win1
 

@@ -122,13 +122,18 @@ FM_API int fm_fine_to_nhwc_bf16(const void* src, int src_dtype, int B, int C, in
  * down_w [Cf,Cc], down_b [Cf], merge_w [Cf,2Cf], merge_b [Cf] fp32, or all NULL when
  * fine_concat_coarse_feat is off.  `count` points at the match count on the device (status word
  * of fm_coarse_match) so no host round-trip is needed; entries >= *count are not touched.
- * win0/win1: [capacity, W*W, Cf] in out_dtype.  Cf must be 64, W*W <= 64. */
+ * win0/win1: [capacity, W*W, Cf] in out_dtype.  Cf must be 64, W*W <= 64.
+ * With merge parameters the work runs on the tensor cores (fp32 weights as 3-term bf16 splits, so
+ * products are fp32-grade) and needs `workspace` of fm_fine_gather_workspace_bytes(...) bytes
+ * (16-byte aligned); without them it is a pure copy and workspace may be NULL. */
+FM_API size_t fm_fine_gather_workspace_bytes(int B, int N0, int N1, int Cc, int Cf, int featc_dtype);
 FM_API int fm_fine_gather(const void* feat_f0, const void* feat_f1, const void* feat_c0,
                    const void* feat_c1, int featc_dtype, const int64_t* b_ids, const int64_t* i_ids,
                    const int64_t* j_ids, const int32_t* count, int capacity, int B, int Hf, int Wf,
                    int Cf, int N0, int N1, int Cc, int w0c, int w1c, int stride, int pad, int W,
                    const float* down_w, const float* down_b, const float* merge_w,
-                   const float* merge_b, void* win0, void* win1, int out_dtype, void* stream);
+                   const float* merge_b, void* win0, void* win1, int out_dtype, void* workspace,
+                   size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------- fine stage: matching
  * FineMatching (dual correlate): mixed centre descriptor of each window against the OTHER

@@ -6,6 +6,6 @@ tail -c 3000 gpurun_out/bench.json; tail -n 20 gpurun_out/bench.err
 python bench.py --impl reference --steps 10 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref exit $?"
 cat gpurun_out/bench_ref.json
 python bench.py --steps 2 --warmup 3 --e2e-steps 0 --no-cpu-baseline > gpurun_out/plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv \
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"coarse_|finish_lse|cand_|blocksum|emit_kernel|fine_|window_merge|ctx_gemm|fold_kernel|cast_bf16|pack_matches|to_nhwc" -c 200 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 2 --warmup 3 --e2e-steps 0 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1
 echo "ncu launches exit $?"
