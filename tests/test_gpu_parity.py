@@ -270,3 +270,60 @@ def test_match_head_end_to_end_vs_oracle():
     assert compare.check_coarse(data, ref, o64["conf_matrix"]) == 0
     assert data["b_ids"].numel() > 2000
     compare.check_fine(data["mkpts0_f"], data["mkpts1_f"], ref["mkpts0_f"], ref["mkpts1_f"])
+
+
+# ------------------------------------------------------------------------------ sync-free pipeline
+@pytest.mark.parametrize("window_dtype", [torch.float32, torch.bfloat16])
+def test_match_head_pipeline_records(window_dtype):
+    """MatchHead.run (count stays on the device) and the host-buffer entry point return the same
+    matches as the oracle, packed as 40-byte records."""
+    from featurematching_b200 import pipeline
+    hw_c, hw_f, hw_i = (24, 32), (96, 128), (192, 256)
+    N, B = 24 * 32, 3
+    fc0, fc1, _ = synth.coarse_features(B, N, N, 256, 0.1, "planted", 21)
+    ff0, ff1 = synth.fine_features(B, 64, hw_f[0], hw_f[1], 22)
+    p = synth.hot_path_params(seed=23)
+    head = pipeline.MatchHead(CFG, DEV, window_dtype=window_dtype)
+    head.load_params(p)
+    rec, h2d, d2h = head.match_host(fc0.pin_memory(), fc1.pin_memory(), ff0.pin_memory(), ff1.pin_memory(),
+                                    hw_i, hw_c, hw_c, hw_f, pair_offset=100)
+    ref = mo.match_head(fc0, fc1, ff0, ff1, hw_i, hw_c, hw_c, hw_f, CFG["match_coarse"], p, p)
+    M = ref["b_ids"].numel()
+    assert len(rec) == M and M > 500
+    assert h2d == sum(t.numel() * t.element_size() for t in (fc0, fc1, ff0, ff1))
+    assert np.array_equal(rec["pair"], ref["b_ids"].numpy() + 100)
+    assert np.array_equal(rec["i"], ref["i_ids"].numpy()) and np.array_equal(rec["j"], ref["j_ids"].numpy())
+    np.testing.assert_allclose(rec["conf"], ref["mconf"].numpy(), rtol=1e-3)
+    ours0 = torch.from_numpy(np.stack([rec["x0"], rec["y0"], rec["std0"]], 1))
+    ours1 = torch.from_numpy(np.stack([rec["x1"], rec["y1"], rec["std1"]], 1))
+    if window_dtype == torch.float32:
+        compare.check_fine(ours0, ours1, ref["mkpts0_f"], ref["mkpts1_f"])
+    else:   # bf16 windows are an opt-in bandwidth saver, outside the 1e-3 px parity contract
+        assert (ours0[:, :2] - ref["mkpts0_f"][:, :2]).abs().max() < 0.1
+    # second call reuses every buffer and gives identical records
+    rec2, _, _ = head.match_host(fc0.pin_memory(), fc1.pin_memory(), ff0.pin_memory(), ff1.pin_memory(),
+                                 hw_i, hw_c, hw_c, hw_f, pair_offset=100)
+    assert np.array_equal(rec2.view(np.uint8), rec.view(np.uint8))
+
+
+def test_gather_large_batch_vs_oracle_windows():
+    """Tensor-core window merge against the oracle on > 1 CTA-round of windows, odd match count,
+    all four map corners (zero padding on every side) and fp32 coarse tokens."""
+    hw_c, hw_f = (16, 20), (64, 80)
+    N, B, M = 320, 2, 1501
+    g = torch.Generator().manual_seed(5)
+    fc0, fc1, _ = synth.coarse_features(B, N, N, 256, 0.1, "planted", 31)
+    ff0, ff1 = synth.fine_features(B, 64, hw_f[0], hw_f[1], 32)
+    corners = torch.tensor([0, hw_c[1] - 1, N - hw_c[1], N - 1])
+    i_ids = torch.cat([corners, torch.randint(0, N, (M - 4,), generator=g)])
+    j_ids = torch.cat([corners.flip(0), torch.randint(0, N, (M - 4,), generator=g)])
+    b_ids = torch.randint(0, B, (M,), generator=g)
+    p = synth.hot_path_params(seed=33)
+    pre, _ = fine_modules(p)
+    data = {"hw0_c": hw_c, "hw1_c": hw_c, "hw0_f": hw_f, "b_ids": b_ids.to(DEV), "i_ids": i_ids.to(DEV),
+            "j_ids": j_ids.to(DEV)}
+    r0, r1 = mo.fine_preprocess(ff0, ff1, fc0, fc1, b_ids, i_ids, j_ids, hw_c, hw_c, hw_f, 7, p)
+    for tok_dtype in (torch.bfloat16, torch.float32):
+        w0, w1 = pre(ff0.to(DEV), ff1.to(DEV), fc0.to(DEV, tok_dtype), fc1.to(DEV, tok_dtype), data)
+        compare.check_windows(w0, r0)
+        compare.check_windows(w1, r1)
