@@ -52,39 +52,51 @@ __global__ void __launch_bounds__(256) finish_lse_kernel(CoarseDims d, float a2,
 }
 
 // ---------------------------------------------------------------- 2. candidates
+// K1 leaves "hot chunk" records in one pool per CTA: (row, first column / 32) + the 32 raw dot
+// products.  One warp per record, one lane per entry; entries that do not exist (j >= N1) or
+// whose confidence is below the threshold drop out here.
 struct CandView {
     int b, i, j;
     float conf;
 };
 
-__device__ __forceinline__ CandView load_candidate(const CoarseDims& d, const uint2* __restrict__ cand,
+__device__ __forceinline__ CandView load_candidate(const CoarseDims& d, float a2, const uint2* __restrict__ meta,
+                                                   const float* __restrict__ dots,
                                                    const float* __restrict__ l2row,
-                                                   const float* __restrict__ l2col, int u, int slot) {
+                                                   const float* __restrict__ l2col, size_t rec, int lane) {
     CandView c;
-    const uint2 rec = cand[static_cast<size_t>(u) * d.cand_cap + slot];
-    const int ms = u % d.S, nblk = (u / d.S) % d.NB;
-    c.b = u / (d.S * d.NB);
-    c.i = ms * d.tiles_per_split * kTileM + static_cast<int>(rec.x >> 8);
-    c.j = nblk * kBlockN + static_cast<int>(rec.x & 0xff);
-    const float t = __uint_as_float(rec.y);
-    const float lr = l2row[static_cast<size_t>(c.b) * d.N0 + c.i];
-    const float lc = l2col[static_cast<size_t>(c.b) * d.N1 + c.j];
-    // conf = softmax_j * softmax_i = 2^(t - lr) * 2^(t - lc)
-    c.conf = exp2f((t - lr) + (t - lc));
+    const uint2 m = meta[rec];
+    c.b = static_cast<int>(m.x / static_cast<uint32_t>(d.N0));
+    c.i = static_cast<int>(m.x - static_cast<uint32_t>(c.b) * d.N0);
+    c.j = static_cast<int>(m.y) * kHotChunk + lane;
+    c.conf = 0.f;
+    if (c.j < d.N1) {
+        const float t = dots[rec * kHotChunk + lane] * a2;
+        const float lr = l2row[static_cast<size_t>(c.b) * d.N0 + c.i];
+        const float lc = l2col[static_cast<size_t>(c.b) * d.N1 + c.j];
+        // conf = softmax_j * softmax_i = 2^(t - lr) * 2^(t - lc)
+        c.conf = exp2f((t - lr) + (t - lc));
+    }
     return c;
 }
 
-__global__ void __launch_bounds__(128) cand_best_kernel(CoarseDims d, float thr, const uint2* __restrict__ cand,
-                                                        const int* __restrict__ unit_count,
+constexpr int kCandBlocksPerPool = 4;
+constexpr int kCandWarps = 8;
+
+__global__ void __launch_bounds__(kCandWarps * 32) cand_best_kernel(CoarseDims d, float a2, float thr,
+                                                        const uint2* __restrict__ meta,
+                                                        const float* __restrict__ dots,
+                                                        const int* __restrict__ hot_count,
                                                         const float* __restrict__ l2row,
                                                         const float* __restrict__ l2col,
                                                         unsigned* __restrict__ rowbest,
                                                         unsigned* __restrict__ colbest, int* __restrict__ status) {
-    // one block per work unit of K1
-    const int u = blockIdx.x, n = min(unit_count[u], d.cand_cap);
-    if (threadIdx.x == 0 && n) atomicAdd(status + kStCandTotal, n);
-    for (int slot = threadIdx.x; slot < n; slot += blockDim.x) {
-        const CandView c = load_candidate(d, cand, l2row, l2col, u, slot);
+    const int pool = blockIdx.x / kCandBlocksPerPool, sub = blockIdx.x % kCandBlocksPerPool;
+    const int n = min(hot_count[pool], d.hot_cap);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0 && sub == 0 && n) atomicAdd(status + kStCandTotal, n);
+    for (int r = sub * kCandWarps + warp; r < n; r += kCandBlocksPerPool * kCandWarps) {
+        const CandView c = load_candidate(d, a2, meta, dots, l2row, l2col, static_cast<size_t>(pool) * d.hot_cap + r, lane);
         if (c.conf > thr) {   // positive floats order like their bit patterns
             atomicMax(rowbest + static_cast<size_t>(c.b) * d.N0 + c.i, __float_as_uint(c.conf));
             atomicMax(colbest + static_cast<size_t>(c.b) * d.N1 + c.j, __float_as_uint(c.conf));
@@ -98,18 +110,21 @@ __device__ __forceinline__ bool interior(int idx, int h, int w, int border) {
     return r >= border && r < h - border && c >= border && c < w - border;
 }
 
-__global__ void __launch_bounds__(128) cand_select_kernel(CoarseDims d, float thr, int h0c, int w0c, int h1c,
-                                                          int w1c, int border, const uint2* __restrict__ cand,
-                                                          const int* __restrict__ unit_count,
+__global__ void __launch_bounds__(kCandWarps * 32) cand_select_kernel(CoarseDims d, float a2, float thr, int h0c, int w0c, int h1c,
+                                                          int w1c, int border, const uint2* __restrict__ meta,
+                                                          const float* __restrict__ dots,
+                                                          const int* __restrict__ hot_count,
                                                           const float* __restrict__ l2row,
                                                           const float* __restrict__ l2col,
                                                           const unsigned* __restrict__ rowbest,
                                                           const unsigned* __restrict__ colbest,
                                                           int* __restrict__ rowcnt, int2* __restrict__ rowslot,
                                                           int* __restrict__ status) {
-    const int u = blockIdx.x, n = min(unit_count[u], d.cand_cap);
-    for (int slot = threadIdx.x; slot < n; slot += blockDim.x) {
-        const CandView c = load_candidate(d, cand, l2row, l2col, u, slot);
+    const int pool = blockIdx.x / kCandBlocksPerPool, sub = blockIdx.x % kCandBlocksPerPool;
+    const int n = min(hot_count[pool], d.hot_cap);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int r = sub * kCandWarps + warp; r < n; r += kCandBlocksPerPool * kCandWarps) {
+        const CandView c = load_candidate(d, a2, meta, dots, l2row, l2col, static_cast<size_t>(pool) * d.hot_cap + r, lane);
         if (!(c.conf > thr)) continue;
         const unsigned bits = __float_as_uint(c.conf);
         const size_t row = static_cast<size_t>(c.b) * d.N0 + c.i;
@@ -228,12 +243,12 @@ cudaError_t launch_coarse_resolve(const CoarseResolveParams& p, const CoarseWork
     const int nmax = d.N0 > d.N1 ? d.N0 : d.N1;
     finish_lse_kernel<<<dim3((nmax + 255) / 256, d.B), 256, 0, st>>>(d, p.a2, w.norm0, w.maxnorm, w.rowpart,
                                                                      w.colpart, w.l2row, w.l2col, p.status);
-    const unsigned cgrid = static_cast<unsigned>(d.num_units);
-    cand_best_kernel<<<cgrid, 128, 0, st>>>(d, p.thr, w.cand, w.unit_count, w.l2row, w.l2col, w.rowbest,
-                                            w.colbest, p.status);
-    cand_select_kernel<<<cgrid, 128, 0, st>>>(d, p.thr, p.h0c, p.w0c, p.h1c, p.w1c, p.border, w.cand,
-                                              w.unit_count, w.l2row, w.l2col, w.rowbest, w.colbest, w.rowcnt,
-                                              w.rowslot, p.status);
+    const unsigned cgrid = static_cast<unsigned>(d.num_pools) * kCandBlocksPerPool;
+    cand_best_kernel<<<cgrid, kCandWarps * 32, 0, st>>>(d, p.a2, p.thr, w.hot_meta, w.hot_dots, w.hot_count, w.l2row,
+                                                        w.l2col, w.rowbest, w.colbest, p.status);
+    cand_select_kernel<<<cgrid, kCandWarps * 32, 0, st>>>(d, p.a2, p.thr, p.h0c, p.w0c, p.h1c, p.w1c, p.border,
+                                                          w.hot_meta, w.hot_dots, w.hot_count, w.l2row, w.l2col,
+                                                          w.rowbest, w.colbest, w.rowcnt, w.rowslot, p.status);
     const int nrows = d.B * d.N0;
     const int nblocks = (nrows + kScanBlock - 1) / kScanBlock;
     row_blocksum_kernel<<<nblocks, kScanBlock, 0, st>>>(w.rowcnt, nrows, w.blocksum);

@@ -67,14 +67,14 @@ __global__ void __launch_bounds__(256) coarse_stats_simt_kernel(const __nv_bfloa
                 rowsum += pij;
                 colsum[c] += pij * wi;
             } else if (pij > p.cand_thr * full) {
-                const int nblk = j / kBlockN;
-                const int u = (b * d.NB + nblk) * d.S + ms;
-                const int slot = atomicAdd(p.unit_count + u, 1);
-                if (slot < d.cand_cap) {
-                    const uint32_t rin = static_cast<uint32_t>(i - ms * d.tiles_per_split * kTileM);
-                    p.cand[static_cast<size_t>(u) * d.cand_cap + slot] =
-                        make_uint2((rin << 8) | static_cast<uint32_t>(j - nblk * kBlockN),
-                                   __float_as_uint(acc[r][c] * p.a2));
+                // one record per entry: the other 31 dots are -inf (confidence 0 in K2)
+                const int pool = static_cast<int>((blockIdx.x + blockIdx.y * gridDim.x + blockIdx.z * 7u) % d.num_pools);
+                const int slot = atomicAdd(p.hot_count + pool, 1);
+                if (slot < d.hot_cap) {
+                    const size_t rec = static_cast<size_t>(pool) * d.hot_cap + slot;
+                    p.hot_meta[rec] = make_uint2(static_cast<uint32_t>(b * d.N0 + i), static_cast<uint32_t>(j / kHotChunk));
+                    for (int k = 0; k < kHotChunk; ++k)
+                        p.hot_dots[rec * kHotChunk + k] = (k == j % kHotChunk) ? acc[r][c] : -INFINITY;
                 } else {
                     atomicOr(p.status + kStFlags, FM_FLAG_CAND_OVERFLOW);
                 }

@@ -7,8 +7,9 @@
 // resolve kernels finish) plus the short list of entries that can exceed the threshold.
 //
 // Work unit = (pair b, block of 256 image-1 tokens, contiguous range of 128-token image-0 tiles).
-// The image-1 block is the RESIDENT MMA operand (B, K-major, 128 KB of smem for C = 256); the
-// image-0 tiles stream through a 5-stage TMA ring as the A operand.  Each tile is one
+// The image-1 block is the RESIDENT MMA operand (B, K-major, 4 x 32 KB channel chunks, each with
+// its own full/empty barrier so the next unit's block streams in behind the last tile's MMAs);
+// the image-0 tiles stream through a 5-stage TMA ring as the A operand.  Each tile is one
 // 128 x 256 x C tcgen05.mma accumulation into one of two 256-column TMEM buffers.
 //
 // Threads: 12 warps = 3 warpgroups.  Warpgroup 0 is control (warp 0 TMA producer, warp 1 MMA
@@ -20,11 +21,13 @@
 //   row  : rowsum += p                   -> rowpart[b][2 nblk + g][i]          (one store per tile)
 //   col  : colacc[j] += p * 2^(c_i - cmax)   thread-local over ALL streamed tiles of the unit,
 //                                        reduced across the 128 rows once per unit -> colpart
-//   cand : an entry with softmax_j share > kCandMargin * thr of its own 128-column partial sum
-//          is pushed to the unit's candidate list (found by re-reading the hot 32-column chunk
-//          from TMEM; rare).  conf > thr implies share > thr of the FULL row sum, so the list
-//          is a superset of everything the resolve step needs.
-// One MUFU.EX2 per score; scale/bias, row sum and column accumulate are packed f32x2 ops.
+//   hot  : a 32-column chunk whose largest p exceeds kCandMargin * thr of the row's own
+//          128-column partial sum is a "hot chunk": its 32 raw dot products are re-read from
+//          TMEM and stored (128 B) with (row, chunk) in the CTA's record pool.  conf > thr implies
+//          share > thr of the FULL row sum, so the pools hold a superset of everything the
+//          resolve step needs; K2 evaluates the 32 entries exactly.
+// One MUFU.EX2 per score; scale/bias, row sum and column accumulate are packed f32x2 ops; the
+// TMEM loads are double-buffered in registers (chunk k+1 in flight while chunk k is processed).
 #include <cuda.h>
 
 #include "fm_common.cuh"
@@ -35,45 +38,49 @@ namespace fm {
 
 namespace {
 
+constexpr int kKC = kMaxC / kChunkK;   // channel chunks of the resident operand (4)
+
 struct __align__(16) SmemCtl {
     float colscratch[kEpiWarps][128];   // first: float4 stores need 16-byte alignment
     uint64_t a_full[kAStages];
     uint64_t a_empty[kAStages];
-    uint64_t b_full;
-    uint64_t b_empty;
+    uint64_t b_full[kKC];
+    uint64_t b_empty[kKC];
     uint64_t t_full[2];
     uint64_t t_empty[2];
     uint32_t tmem_base;
-    int cand_count;
+    int hot_count;
 };
 
-constexpr size_t kSmemOperands = static_cast<size_t>(kBChunkBytes) * (kMaxC / kChunkK) +
+constexpr size_t kSmemOperands = static_cast<size_t>(kBChunkBytes) * kKC +
                                  static_cast<size_t>(kAStageBytes) * kAStages;
 constexpr size_t kSmemBytes = kSmemOperands + sizeof(SmemCtl) + 1024;  // + alignment slack
 static_assert(kSmemBytes <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
 
-// One 32-column chunk of the thread's accumulator row.
-template <bool kMasked>
-__device__ __forceinline__ void process_chunk(const uint32_t (&r)[32], uint64_t a2p, uint64_t biasp,
-                                              uint64_t wp, uint64_t* colacc, uint64_t& racc0,
-                                              uint64_t& racc1, float& cmax, int nvalid_in_chunk) {
+// One 32-column chunk of the thread's accumulator row; returns the chunk's largest p.
+__device__ __forceinline__ float process_chunk(const uint32_t (&r)[32], uint64_t a2p, uint64_t biasp,
+                                               uint64_t wp, uint64_t* colacc, uint64_t& racc0,
+                                               uint64_t& racc1) {
     float m = 0.f;
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
         uint64_t t2 = fma2(pack2(__uint_as_float(r[2 * k]), __uint_as_float(r[2 * k + 1])), a2p, biasp);
         float tl, th;
         unpack2(t2, tl, th);
-        float pl = ex2_approx(tl), ph = ex2_approx(th);
-        if constexpr (kMasked) {
-            pl = (2 * k < nvalid_in_chunk) ? pl : 0.f;
-            ph = (2 * k + 1 < nvalid_in_chunk) ? ph : 0.f;
-        }
-        uint64_t p2 = pack2(pl, ph);
+        const float pl = ex2_approx(tl), ph = ex2_approx(th);
+        const uint64_t p2 = pack2(pl, ph);
         if (k & 1) racc1 = add2(racc1, p2); else racc0 = add2(racc0, p2);
         colacc[k] = fma2(p2, wp, colacc[k]);
         m = max3(m, pl, ph);
     }
-    cmax = m;
+    return m;
+}
+
+// Columns >= nv of the chunk do not exist (N1 is not a multiple of the block): make their
+// scores -inf so that p = 0.  Warp-uniform, only ever taken in the last block of a pair.
+__device__ __forceinline__ void mask_chunk(uint32_t (&r)[32], int nv) {
+#pragma unroll
+    for (int k = 0; k < 32; ++k) r[k] = (k < nv) ? r[k] : 0xff800000u;
 }
 
 // One butterfly step of the transposing reduction of 2*kHalf per-thread column sums across
@@ -96,7 +103,7 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smem_b = smem;                                            // KC x 32 KB, resident
-    uint8_t* smem_a = smem + static_cast<size_t>(kBChunkBytes) * (kMaxC / kChunkK);  // ring
+    uint8_t* smem_a = smem + static_cast<size_t>(kBChunkBytes) * kKC;  // ring
     SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem + kSmemOperands);
 
     const CoarseDims& d = p.d;
@@ -105,10 +112,9 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kAStages; ++s) { mbar_init(&ctl->a_full[s], 1); mbar_init(&ctl->a_empty[s], 1); }
-        mbar_init(&ctl->b_full, 1);
-        mbar_init(&ctl->b_empty, 1);
+        for (int s = 0; s < kKC; ++s) { mbar_init(&ctl->b_full[s], 1); mbar_init(&ctl->b_empty[s], 1); }
         for (int s = 0; s < 2; ++s) { mbar_init(&ctl->t_full[s], 1); mbar_init(&ctl->t_empty[s], kEpiWarps); }
-        ctl->cand_count = 0;
+        ctl->hot_count = 0;
         fence_mbar_init();
         tma_prefetch_desc(&tmap0);
         tma_prefetch_desc(&tmap1);
@@ -120,7 +126,8 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
     const uint32_t tmem_base = ctl->tmem_base;
 
     // Register re-balancing between warpgroups: the control warpgroup keeps 40 registers per
-    // thread, the two epilogue warpgroups grow to 232 (128 live column accumulators each).
+    // thread, the two epilogue warpgroups grow to 232 (128 column accumulators + two 32-word
+    // TMEM load buffers each).
     if (warp < kCtlWarps) {
     reg_dealloc<40>();
     if (warp == 0) {
@@ -131,13 +138,16 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                 const int ms = u % d.S, nblk = (u / d.S) % d.NB, b = u / (d.S * d.NB);
                 const int mt0 = ms * d.tiles_per_split;
                 const int mt1 = min(mt0 + d.tiles_per_split, d.MT);
-                mbar_wait(&ctl->b_empty, (unit_it & 1) ^ 1);
-                mbar_arrive_expect_tx(&ctl->b_full, static_cast<uint32_t>(kBChunkBytes) * KC);
-                for (int kc = 0; kc < KC; ++kc)
-                    tma_load_3d(smem_b + static_cast<size_t>(kc) * kBChunkBytes, &tmap1, &ctl->b_full,
-                                kc * kChunkK, nblk * kBlockN, b);
                 for (int mt = mt0; mt < mt1; ++mt) {
                     for (int kc = 0; kc < KC; ++kc, ++a_it) {
+                        if (mt == mt0) {
+                            // chunk kc of the new resident block, as soon as the previous unit's
+                            // last MMAs on that chunk have retired
+                            mbar_wait(&ctl->b_empty[kc], (unit_it & 1) ^ 1);
+                            mbar_arrive_expect_tx(&ctl->b_full[kc], kBChunkBytes);
+                            tma_load_3d(smem_b + static_cast<size_t>(kc) * kBChunkBytes, &tmap1, &ctl->b_full[kc],
+                                        kc * kChunkK, nblk * kBlockN, b);
+                        }
                         const uint32_t s = a_it % kAStages, ph = (a_it / kAStages) & 1;
                         mbar_wait(&ctl->a_empty[s], ph ^ 1);
                         mbar_arrive_expect_tx(&ctl->a_full[s], kAStageBytes);
@@ -157,7 +167,6 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                 const int ms = u % d.S;
                 const int mt0 = ms * d.tiles_per_split;
                 const int mt1 = min(mt0 + d.tiles_per_split, d.MT);
-                mbar_wait(&ctl->b_full, unit_it & 1);
                 for (int mt = mt0; mt < mt1; ++mt, ++tile_it) {
                     const uint32_t buf = tile_it & 1, tph = (tile_it >> 1) & 1;
                     mbar_wait(&ctl->t_empty[buf], tph ^ 1);
@@ -165,6 +174,7 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                     const uint32_t d_tmem = tmem_base + buf * kBlockN;
                     for (int kc = 0; kc < KC; ++kc, ++a_it) {
                         const uint32_t s = a_it % kAStages, ph = (a_it / kAStages) & 1;
+                        if (mt == mt0) mbar_wait(&ctl->b_full[kc], unit_it & 1);
                         mbar_wait(&ctl->a_full[s], ph);
                         tc_fence_after();
                         const uint32_t a_addr = a_base + s * kAStageBytes;
@@ -176,10 +186,10 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                                          (kc | k) != 0 ? 1u : 0u);
                         }
                         umma_commit(&ctl->a_empty[s]);   // frees the A stage once these MMAs retire
+                        if (mt == mt1 - 1) umma_commit(&ctl->b_empty[kc]);   // chunk may be overwritten
                     }
                     umma_commit(&ctl->t_full[buf]);      // accumulator complete
                 }
-                umma_commit(&ctl->b_empty);              // resident block may be overwritten
             }
         }
     }
@@ -191,6 +201,8 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
         const int q = warp & 3;               // TMEM lane quarter this warp may access
         const int et = threadIdx.x - kCtlWarps * 32;   // 0..255
         const uint64_t a2p = pack2(p.a2, p.a2);
+        uint2* const pool_meta = p.hot_meta + static_cast<size_t>(blockIdx.x) * d.hot_cap;
+        float* const pool_dots = p.hot_dots + static_cast<size_t>(blockIdx.x) * d.hot_cap * kHotChunk;
         uint32_t tile_it = 0;
         for (int u = blockIdx.x; u < d.num_units; u += gridDim.x) {
             const int ms = u % d.S, nblk = (u / d.S) % d.NB, b = u / (d.S * d.NB);
@@ -199,9 +211,9 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
             const float maxn0 = p.maxnorm[b * 2 + 0], maxn1 = p.maxnorm[b * 2 + 1];
             const float cref = score_bound2(maxn0, maxn1, p.a2) - kHead2;
             // valid columns of this warpgroup's half of the block
-            const int nvalid = max(0, min(128, d.N1 - nblk * kBlockN - wg * 128));
+            const int col0 = nblk * kBlockN + wg * 128;
+            const int nvalid = max(0, min(128, d.N1 - col0));
             float* rowpart = p.rowpart + (static_cast<size_t>(b) * d.NB * 2 + nblk * 2 + wg) * d.N0pad;
-            uint2* cand = p.cand + static_cast<size_t>(u) * d.cand_cap;
 
             uint64_t colacc[64];
 #pragma unroll
@@ -223,48 +235,54 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
 
                 uint64_t racc0 = 0ull, racc1 = 0ull;
                 float cm[4];
-                uint32_t r[32];
-#pragma unroll
-                for (int ch = 0; ch < 4; ++ch) {
-                    const int nv = nvalid - ch * 32;
-                    if (nv <= 0) { cm[ch] = 0.f; continue; }   // warp-uniform
-                    tmem_ld_32x32(taddr + ch * 32, r);
-                    tmem_ld_wait();
-                    if (nv >= 32) process_chunk<false>(r, a2p, biasp, wp, colacc + ch * 16, racc0, racc1, cm[ch], 32);
-                    else          process_chunk<true>(r, a2p, biasp, wp, colacc + ch * 16, racc0, racc1, cm[ch], nv);
-                }
+                uint32_t ra[32], rb[32];
+                tmem_ld_32x32(taddr, ra);
+                // chunk 0
+                tmem_ld_wait_dep(ra);
+                tmem_ld_32x32(taddr + 32, rb);
+                if (nvalid < 32) mask_chunk(ra, nvalid);
+                cm[0] = process_chunk(ra, a2p, biasp, wp, colacc, racc0, racc1);
+                // chunk 1
+                tmem_ld_wait_dep(rb);
+                tmem_ld_32x32(taddr + 64, ra);
+                if (nvalid < 64) mask_chunk(rb, nvalid - 32);
+                cm[1] = process_chunk(rb, a2p, biasp, wp, colacc + 16, racc0, racc1);
+                // chunk 2
+                tmem_ld_wait_dep(ra);
+                tmem_ld_32x32(taddr + 96, rb);
+                if (nvalid < 96) mask_chunk(ra, nvalid - 64);
+                cm[2] = process_chunk(ra, a2p, biasp, wp, colacc + 32, racc0, racc1);
+                // chunk 3
+                tmem_ld_wait_dep(rb);
+                if (nvalid < 128) mask_chunk(rb, nvalid - 96);
+                cm[3] = process_chunk(rb, a2p, biasp, wp, colacc + 48, racc0, racc1);
+
                 float s0, s1, s2, s3;
                 unpack2(racc0, s0, s1);
                 unpack2(racc1, s2, s3);
                 const float rowsum = (s0 + s1) + (s2 + s3);
                 rowpart[mt * kTileM + q * 32 + lane] = rowsum;
 
-                // ---- candidates: chunks whose maximum exceeds the share threshold (rare)
+                // ---- hot chunks: largest p above the share threshold of the row's partial sum
                 const float share = p.cand_thr * rowsum;
                 uint32_t hot = 0;
 #pragma unroll
                 for (int ch = 0; ch < 4; ++ch) hot |= (cm[ch] > share) ? (1u << ch) : 0u;
-                const uint32_t warp_hot = __reduce_or_sync(0xffffffffu, hot);
-                if (warp_hot) {
-                    for (int ch = 0; ch < 4; ++ch) {
-                        if (!((warp_hot >> ch) & 1)) continue;   // warp-uniform
-                        tmem_ld_32x32(taddr + ch * 32, r);
-                        tmem_ld_wait();
-                        if ((hot >> ch) & 1) {
-                            const int nv = min(32, nvalid - ch * 32);
+                uint32_t warp_hot = __reduce_or_sync(0xffffffffu, hot);
+                while (warp_hot) {                                   // warp-uniform, usually 0 or 1 trips
+                    const int ch = __ffs(warp_hot) - 1;
+                    warp_hot &= warp_hot - 1;
+                    tmem_ld_32x32(taddr + ch * 32, ra);
+                    tmem_ld_wait_dep(ra);
+                    if ((hot >> ch) & 1) {
+                        const int slot = atomicAdd(&ctl->hot_count, 1);
+                        if (slot < d.hot_cap) {
+                            pool_meta[slot] = make_uint2(static_cast<uint32_t>(b * d.N0 + row),
+                                                         static_cast<uint32_t>((col0 >> 5) + ch));
+                            uint4* dst = reinterpret_cast<uint4*>(pool_dots + static_cast<size_t>(slot) * kHotChunk);
 #pragma unroll
-                            for (int k = 0; k < 32; ++k) {
-                                const float dot = __uint_as_float(r[k]);
-                                const float pk = ex2_approx(fmaf(dot, p.a2, bias));
-                                if (k < nv && pk > share) {
-                                    const int slot = atomicAdd(&ctl->cand_count, 1);
-                                    if (slot < d.cand_cap) {
-                                        const uint32_t rin = static_cast<uint32_t>((mt - mt0) * kTileM + q * 32 + lane);
-                                        cand[slot] = make_uint2((rin << 8) | static_cast<uint32_t>(wg * 128 + ch * 32 + k),
-                                                                __float_as_uint(dot * p.a2));
-                                    }
-                                }
-                            }
+                            for (int k = 0; k < 8; ++k)
+                                dst[k] = make_uint4(ra[4 * k], ra[4 * k + 1], ra[4 * k + 2], ra[4 * k + 3]);
                         }
                     }
                 }
@@ -295,15 +313,16 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                 const float s = (ctl->colscratch[g * 4 + 0][c] + ctl->colscratch[g * 4 + 1][c]) +
                                 (ctl->colscratch[g * 4 + 2][c] + ctl->colscratch[g * 4 + 3][c]);
                 p.colpart[(static_cast<size_t>(b) * d.S + ms) * d.N1pad + nblk * kBlockN + et] = s;
-                if (et == 0) {
-                    const int cnt = ctl->cand_count;
-                    p.unit_count[u] = min(cnt, d.cand_cap);
-                    if (cnt > d.cand_cap) atomicOr(p.status + kStFlags, FM_FLAG_CAND_OVERFLOW);
-                    atomicMax(p.status + kStMaxUnitCand, cnt);
-                    ctl->cand_count = 0;
-                }
             }
             named_bar_sync(1, kEpiWarps * 32);
+        }
+        // ---- kernel end: publish the pool's record count
+        named_bar_sync(1, kEpiWarps * 32);
+        if (et == 0) {
+            const int cnt = ctl->hot_count;
+            p.hot_count[blockIdx.x] = min(cnt, d.hot_cap);
+            if (cnt > d.hot_cap) atomicOr(p.status + kStFlags, FM_FLAG_CAND_OVERFLOW);
+            atomicMax(p.status + kStMaxUnitCand, cnt);
         }
     }
 
@@ -364,7 +383,8 @@ cudaError_t launch_coarse_stats_tc(const __nv_bfloat16* f0, const __nv_bfloat16*
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    const int grid = p.d.num_units < num_sms ? p.d.num_units : num_sms;
+    (void)num_sms;
+    const int grid = p.d.num_pools;   // one record pool per CTA
     coarse_stats_tc_kernel<<<grid, kCoarseThreads, kSmemBytes, st>>>(tm0, tm1, p);
     return cudaGetLastError();
 }

@@ -106,7 +106,10 @@ CoarseDims coarse_dims(int B, int N0, int N1, int C, int cand_per_row, int num_s
     d.tiles_per_split = best_tps;
     d.S = (d.MT + best_tps - 1) / best_tps;
     d.num_units = B * d.NB * d.S;
-    d.cand_cap = cand_per_row * d.tiles_per_split * kTileM;
+    d.num_pools = d.num_units < num_sms ? d.num_units : num_sms;
+    // planted / real data give about one hot chunk per image-0 token; cand_per_row = 4 leaves 2x
+    const long long want = (1LL * cand_per_row * B * N0 + 2LL * d.num_pools - 1) / (2LL * d.num_pools) + 64;
+    d.hot_cap = want > (1 << 24) ? (1 << 24) : static_cast<int>(want);
     key[0] = B; key[1] = N0; key[2] = N1; key[3] = C; key[4] = cand_per_row; key[5] = num_sms;
     cached = d;
     return d;
@@ -123,7 +126,7 @@ CoarseWorkspace coarse_workspace(const CoarseDims& d, bool fp32_input, void* bas
     // ---- region cleared at the start of every call
     w.zero_begin = off;
     w.maxnorm = reinterpret_cast<float*>(take(sizeof(float) * B * 2));
-    w.unit_count = reinterpret_cast<int*>(take(sizeof(int) * d.num_units));
+    w.hot_count = reinterpret_cast<int*>(take(sizeof(int) * d.num_pools));
     w.rowbest = reinterpret_cast<unsigned*>(take(sizeof(unsigned) * B * d.N0));
     w.colbest = reinterpret_cast<unsigned*>(take(sizeof(unsigned) * B * d.N1));
     w.rowcnt = reinterpret_cast<int*>(take(sizeof(int) * B * d.N0));
@@ -136,7 +139,8 @@ CoarseWorkspace coarse_workspace(const CoarseDims& d, bool fp32_input, void* bas
     w.l2col = reinterpret_cast<float*>(take(sizeof(float) * B * d.N1));
     w.rowslot = reinterpret_cast<int2*>(take(sizeof(int2) * B * d.N0 * kRowSlots));
     w.blocksum = reinterpret_cast<int*>(take(sizeof(int) * ((B * d.N0 + 1023) / 1024 + 1)));
-    w.cand = reinterpret_cast<uint2*>(take(sizeof(uint2) * static_cast<size_t>(d.num_units) * d.cand_cap));
+    w.hot_meta = reinterpret_cast<uint2*>(take(sizeof(uint2) * static_cast<size_t>(d.num_pools) * d.hot_cap));
+    w.hot_dots = reinterpret_cast<float*>(take(sizeof(float) * kHotChunk * static_cast<size_t>(d.num_pools) * d.hot_cap));
     if (fp32_input) {
         w.f0b = reinterpret_cast<__nv_bfloat16*>(take(sizeof(__nv_bfloat16) * B * d.N0 * d.C));
         w.f1b = reinterpret_cast<__nv_bfloat16*>(take(sizeof(__nv_bfloat16) * B * d.N1 * d.C));
@@ -228,7 +232,7 @@ static int coarse_match_impl(bool simt, const void* feat_c0, const void* feat_c1
     sp.a2 = 1.4426950408889634f / (static_cast<float>(C) * temperature);
     sp.cand_thr = kCandMargin * thr;
     sp.norm0 = w.norm0; sp.maxnorm = w.maxnorm; sp.rowpart = w.rowpart; sp.colpart = w.colpart;
-    sp.cand = w.cand; sp.unit_count = w.unit_count; sp.status = status;
+    sp.hot_meta = w.hot_meta; sp.hot_dots = w.hot_dots; sp.hot_count = w.hot_count; sp.status = status;
     cudaEvent_t ev0, ev1;
     const bool timed = !simt && timer_pair(&ev0, &ev1);
     if (timed) cudaEventRecord(ev0, st);
@@ -322,7 +326,7 @@ int fm_profile_coarse_stats(const void* feat_c0, const void* feat_c1, int B, int
     sp.a2 = 1.4426950408889634f / (static_cast<float>(C) * temperature);
     sp.cand_thr = kCandMargin * thr;
     sp.norm0 = w.norm0; sp.maxnorm = w.maxnorm; sp.rowpart = w.rowpart; sp.colpart = w.colpart;
-    sp.cand = w.cand; sp.unit_count = w.unit_count; sp.status = status;
+    sp.hot_meta = w.hot_meta; sp.hot_dots = w.hot_dots; sp.hot_count = w.hot_count; sp.status = status;
     cudaEvent_t ev0, ev1;
     cudaEventCreate(&ev0);
     cudaEventCreate(&ev1);

@@ -44,8 +44,13 @@ struct CoarseDims {
     int S, tiles_per_split;    // M range split into S contiguous pieces per (pair, N block)
     int num_units;             // B * NB * S
     int N0pad, N1pad;          // MT * 128, NB * 256
-    int cand_cap;              // candidate records per work unit
+    int num_pools;             // hot-chunk record pools (= CTAs of the statistics kernel)
+    int hot_cap;               // records per pool
 };
+
+// A "hot chunk" = 32 consecutive scores of one image-0 token, at least one of which may exceed
+// the confidence threshold.  K1 stores the raw dot products; K2 evaluates all 32 exactly.
+constexpr int kHotChunk = 32;
 
 struct CoarseWorkspace {
     // all pointers into the caller's workspace
@@ -55,8 +60,9 @@ struct CoarseWorkspace {
     float* maxnorm;       // [B, 2] (float bits, atomicMax)
     float* rowpart;       // [B, NB * 2, N0pad]
     float* colpart;       // [B, S, N1pad]
-    uint2* cand;          // [num_units, cand_cap]  x = row_in_unit << 8 | col_in_block, y = score bits
-    int* unit_count;      // [num_units]
+    uint2* hot_meta;      // [num_pools, hot_cap]  x = b * N0 + i, y = first column / 32
+    float* hot_dots;      // [num_pools, hot_cap, 32]  raw <f0_i, f1_j> of the chunk's 32 columns
+    int* hot_count;       // [num_pools]
     float* l2row;         // [B, N0]  log2 sum_j 2^t_ij
     float* l2col;         // [B, N1]
     unsigned* rowbest;    // [B, N0]  float bits of best strong confidence
@@ -76,8 +82,9 @@ struct CoarseStatsParams {
     const float* maxnorm;
     float* rowpart;
     float* colpart;
-    uint2* cand;
-    int* unit_count;
+    uint2* hot_meta;
+    float* hot_dots;
+    int* hot_count;
     int* status;
 };
 
