@@ -350,6 +350,10 @@ def install(net):
     fp.load_state_dict(net.fine_preprocess.state_dict(), strict=False)
     fm.load_state_dict({k: v for k, v in net.fine_matching.state_dict().items()
                         if k.startswith('mix_feat_')}, strict=True)
+    # the replaced modules stay reachable for training (not registered: state_dict is unchanged)
+    object.__setattr__(net, '_fm_reference', {'coarse_matching': net.coarse_matching,
+                                              'fine_preprocess': net.fine_preprocess,
+                                              'fine_matching': net.fine_matching})
     net.coarse_matching = cm.to(dev)
     net.fine_preprocess = fp.to(dev)
     net.fine_matching = fm.to(dev)
