@@ -80,7 +80,7 @@ __device__ __forceinline__ CandView load_candidate(const CoarseDims& d, float a2
     return c;
 }
 
-constexpr int kCandBlocksPerPool = 4;
+constexpr int kCandBlocksPerPool = 16;
 constexpr int kCandWarps = 8;
 
 __global__ void __launch_bounds__(kCandWarps * 32) cand_best_kernel(CoarseDims d, float a2, float thr,

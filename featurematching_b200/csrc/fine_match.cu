@@ -13,6 +13,8 @@
 // current one is reduced.  Phase A gives a lane two channels (conflict-free row reads), phase B
 // gives a lane one window cell and walks the channels in a rotated order (conflict-free 128-bit
 // reads); the 49-way soft-max / expectation reductions are warp shuffles.
+#include <cstdlib>
+
 #include "fm_common.cuh"
 #include "fm_ptx.cuh"
 
@@ -49,24 +51,25 @@ __device__ __forceinline__ float2 load_pair(const __nv_bfloat16* w, int r, int l
     return __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(w)[r * (kC / 2) + lane]);
 }
 
-// <mixed, window row r>, channels visited in a per-row rotated order
+// <mixed, window row r>, channels visited in a per-row rotated order (conflict-free 128-bit
+// reads); four partial sums keep the FMA chains short.
 __device__ __forceinline__ float row_dot(const float* w, const float* mixed, int r) {
     const float4* row = reinterpret_cast<const float4*>(w + r * kC);
     const float4* mx = reinterpret_cast<const float4*>(mixed);
-    float acc = 0.f;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
     for (int k = 0; k < kC / 4; ++k) {
         const int ch = (k + r) & (kC / 4 - 1);
         const float4 x = row[ch], m = mx[ch];
-        acc = fmaf(x.x, m.x, acc); acc = fmaf(x.y, m.y, acc);
-        acc = fmaf(x.z, m.z, acc); acc = fmaf(x.w, m.w, acc);
+        a0 = fmaf(x.x, m.x, a0); a1 = fmaf(x.y, m.y, a1);
+        a2 = fmaf(x.z, m.z, a2); a3 = fmaf(x.w, m.w, a3);
     }
-    return acc;
+    return (a0 + a1) + (a2 + a3);
 }
 __device__ __forceinline__ float row_dot(const __nv_bfloat16* w, const float* mixed, int r) {
     const uint4* row = reinterpret_cast<const uint4*>(w + r * kC);
     const float4* mx = reinterpret_cast<const float4*>(mixed);
-    float acc = 0.f;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
     for (int k = 0; k < kC / 8; ++k) {
         const int ch = (k + r) & (kC / 8 - 1);
@@ -76,30 +79,57 @@ __device__ __forceinline__ float row_dot(const __nv_bfloat16* w, const float* mi
         const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
         const float2 c = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.z));
         const float2 e = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.w));
-        acc = fmaf(a.x, m0.x, acc); acc = fmaf(a.y, m0.y, acc);
-        acc = fmaf(b.x, m0.z, acc); acc = fmaf(b.y, m0.w, acc);
-        acc = fmaf(c.x, m1.x, acc); acc = fmaf(c.y, m1.y, acc);
-        acc = fmaf(e.x, m1.z, acc); acc = fmaf(e.y, m1.w, acc);
+        a0 = fmaf(a.x, m0.x, a0); a1 = fmaf(a.y, m0.y, a1);
+        a2 = fmaf(b.x, m0.z, a2); a3 = fmaf(b.y, m0.w, a3);
+        a0 = fmaf(c.x, m1.x, a0); a1 = fmaf(c.y, m1.y, a1);
+        a2 = fmaf(e.x, m1.z, a2); a3 = fmaf(e.y, m1.w, a3);
     }
-    return acc;
+    return (a0 + a1) + (a2 + a3);
 }
 
-// soft-max over the WW cells held as (sa: cell lane, sb: cell lane + 32), then expectation / std
-__device__ __forceinline__ void heat_stats(float sa, float sb, bool has_b, float ga_x, float ga_y, float gb_x,
-                                           float gb_y, float temp, float& ex, float& ey, float& sd) {
-    const float ta = sa * temp, tb = has_b ? sb * temp : -INFINITY;
-    const float mx = warp_max(fmaxf(ta, tb));
-    const float ea = expf(ta - mx), eb = has_b ? expf(tb - mx) : 0.f;
-    const float sum = warp_sum(ea + eb);
-    const float ha = ea / sum, hb = eb / sum;
-    ex = warp_sum(fmaf(ga_x, ha, gb_x * hb));
-    ey = warp_sum(fmaf(ga_y, ha, gb_y * hb));
-    const float vx = warp_sum(fmaf(ga_x * ga_x, ha, gb_x * gb_x * hb)) - ex * ex;
-    const float vy = warp_sum(fmaf(ga_y * ga_y, ha, gb_y * gb_y * hb)) - ey * ey;
-    sd = sqrtf(fmaxf(vx, 1e-10f)) + sqrtf(fmaxf(vy, 1e-10f));
+// Soft-max over the WW cells of BOTH heat maps (cells lane and lane + 32), then expectation and
+// std.  The ten moment sums (sum, x, y, x^2, y^2 per map) are un-normalised and reduced side by
+// side, so the whole thing is two dependent butterflies instead of twelve.
+struct HeatOut { float ex, ey, sd; };
+__device__ __forceinline__ void heat_stats2(float s0a, float s0b, float s1a, float s1b, bool has_a, bool has_b,
+                                            float ga_x, float ga_y, float gb_x, float gb_y, float temp,
+                                            HeatOut& h0, HeatOut& h1) {
+    const float t0a = has_a ? s0a * temp : -INFINITY, t0b = has_b ? s0b * temp : -INFINITY;
+    const float t1a = has_a ? s1a * temp : -INFINITY, t1b = has_b ? s1b * temp : -INFINITY;
+    float m0 = fmaxf(t0a, t0b), m1 = fmaxf(t1a, t1b);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, o));
+        m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, o));
+    }
+    const float e0a = has_a ? expf(t0a - m0) : 0.f, e0b = has_b ? expf(t0b - m0) : 0.f;
+    const float e1a = has_a ? expf(t1a - m1) : 0.f, e1b = has_b ? expf(t1b - m1) : 0.f;
+    float v[10];
+    v[0] = e0a + e0b;
+    v[1] = fmaf(ga_x, e0a, gb_x * e0b);
+    v[2] = fmaf(ga_y, e0a, gb_y * e0b);
+    v[3] = fmaf(ga_x * ga_x, e0a, gb_x * gb_x * e0b);
+    v[4] = fmaf(ga_y * ga_y, e0a, gb_y * gb_y * e0b);
+    v[5] = e1a + e1b;
+    v[6] = fmaf(ga_x, e1a, gb_x * e1b);
+    v[7] = fmaf(ga_y, e1a, gb_y * e1b);
+    v[8] = fmaf(ga_x * ga_x, e1a, gb_x * gb_x * e1b);
+    v[9] = fmaf(ga_y * ga_y, e1a, gb_y * gb_y * e1b);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int k = 0; k < 10; ++k) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+    }
+    const float i0 = 1.f / v[0], i1 = 1.f / v[5];
+    h0.ex = v[1] * i0; h0.ey = v[2] * i0;
+    h1.ex = v[6] * i1; h1.ey = v[7] * i1;
+    const float vx0 = v[3] * i0 - h0.ex * h0.ex, vy0 = v[4] * i0 - h0.ey * h0.ey;
+    const float vx1 = v[8] * i1 - h1.ex * h1.ex, vy1 = v[9] * i1 - h1.ey * h1.ey;
+    h0.sd = sqrtf(fmaxf(vx0, 1e-10f)) + sqrtf(fmaxf(vy0, 1e-10f));
+    h1.sd = sqrtf(fmaxf(vx1, 1e-10f)) + sqrtf(fmaxf(vy1, 1e-10f));
 }
 
-template <typename T, int kWarps>
+template <typename T, int kWarps, int kStages>
 __global__ void __launch_bounds__(kWarps * 32) fine_match_kernel(
     const T* __restrict__ win0, const T* __restrict__ win1, const float* __restrict__ mkpts0_c,
     const float* __restrict__ mkpts1_c, const float* __restrict__ mix_w0, const float* __restrict__ mix_b0,
@@ -108,20 +138,19 @@ __global__ void __launch_bounds__(kWarps * 32) fine_match_kernel(
     extern __shared__ __align__(128) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t win_bytes = static_cast<uint32_t>(WW) * kC * sizeof(T);
-    // layout: [kWarps][2 stages][2 windows][win_bytes] | mixed [kWarps][2][64] f32 | weights [2][64] | bars
-    uint8_t* ring = smem + static_cast<size_t>(warp) * 4 * win_bytes;
-    float* fbase = reinterpret_cast<float*>(smem + static_cast<size_t>(kWarps) * 4 * win_bytes);
+    // layout: [kWarps][kStages][2 windows][win_bytes] | mixed [kWarps][2][64] f32 | weights [2][64] | bars
+    uint8_t* ring = smem + static_cast<size_t>(warp) * kStages * 2 * win_bytes;
+    float* fbase = reinterpret_cast<float*>(smem + static_cast<size_t>(kWarps) * kStages * 2 * win_bytes);
     float* mixed = fbase + warp * 2 * kC;
     float* wts = fbase + kWarps * 2 * kC;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(wts + 2 * kMaxWW) + warp * 2;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(wts + 2 * kMaxWW) + warp * kStages;
 
     for (int k = threadIdx.x; k < 2 * kMaxWW; k += blockDim.x) {
         const int r = k & (kMaxWW - 1);
         wts[k] = r < WW ? (k < kMaxWW ? mix_w0[r] : mix_w1[r]) : 0.f;
     }
     if (lane == 0) {
-        mbar_init(&bars[0], 1);
-        mbar_init(&bars[1], 1);
+        for (int k = 0; k < kStages; ++k) mbar_init(&bars[k], 1);
         fence_mbar_init();
     }
     __syncthreads();
@@ -144,37 +173,62 @@ __global__ void __launch_bounds__(kWarps * 32) fine_match_kernel(
         bulk_g2s(dst, win0 + static_cast<size_t>(m) * WW * kC, win_bytes, &bars[stage]);
         bulk_g2s(dst + win_bytes, win1 + static_cast<size_t>(m) * WW * kC, win_bytes, &bars[stage]);
     };
-    if (gw < M && lane == 0) issue(0, gw);
+    // ring of kStages matches per warp: kStages - 1 copies in flight while one match is reduced
+    // (kStages == 1: the copy of the current match is issued and awaited, other warps overlap)
+    if (lane == 0)
+        for (int k = 0; k + 1 < kStages; ++k)
+            if (gw + k * nw < M) issue(k, gw + k * nw);
     uint32_t it = 0;
     for (int m = gw; m < M; m += nw, ++it) {
-        const int s = it & 1;
-        if (m + nw < M && lane == 0) issue(s ^ 1, m + nw);
-        mbar_wait(&bars[s], (it >> 1) & 1);
+        const int s = it % kStages;
+        {
+            const int mn = m + (kStages - 1) * nw;
+            if (mn < M && lane == 0) issue((it + kStages - 1) % kStages, mn);
+        }
+        // coarse coordinates of this match: loaded now, consumed after the reductions
+        float2 c0 = make_float2(0.f, 0.f), c1 = make_float2(0.f, 0.f);
+        if (lane == 0) {
+            c0 = __ldg(reinterpret_cast<const float2*>(mkpts0_c) + m);
+            c1 = __ldg(reinterpret_cast<const float2*>(mkpts1_c) + m);
+        }
+        mbar_wait(&bars[s], (it / kStages) & 1);
         const T* w0 = reinterpret_cast<const T*>(ring + static_cast<size_t>(s) * 2 * win_bytes);
         const T* w1 = reinterpret_cast<const T*>(ring + static_cast<size_t>(s) * 2 * win_bytes + win_bytes);
 
-        // ---- phase A: mixed centre descriptors, two channels per lane
+        // ---- phase A: mixed centre descriptors, two channels per lane; even / odd rows go to
+        // separate accumulators and the loop is unrolled so the row loads are in flight together
         float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
-        for (int r = 0; r < WW; ++r) {
+        float2 c0e = make_float2(0.f, 0.f), c1e = make_float2(0.f, 0.f);
+#pragma unroll 8
+        for (int r = 0; r + 1 < WW; r += 2) {
+            const float2 x0 = load_pair(w0, r, lane), x1 = load_pair(w1, r, lane);
+            const float2 y0 = load_pair(w0, r + 1, lane), y1 = load_pair(w1, r + 1, lane);
+            const float2 u0 = *reinterpret_cast<const float2*>(wts + r);
+            const float2 u1 = *reinterpret_cast<const float2*>(wts + kMaxWW + r);
+            a0.x = fmaf(u0.x, x0.x, a0.x); a0.y = fmaf(u0.x, x0.y, a0.y);
+            a1.x = fmaf(u1.x, x1.x, a1.x); a1.y = fmaf(u1.x, x1.y, a1.y);
+            c0e.x = fmaf(u0.y, y0.x, c0e.x); c0e.y = fmaf(u0.y, y0.y, c0e.y);
+            c1e.x = fmaf(u1.y, y1.x, c1e.x); c1e.y = fmaf(u1.y, y1.y, c1e.y);
+        }
+        if (WW & 1) {
+            const int r = WW - 1;
             const float2 x0 = load_pair(w0, r, lane), x1 = load_pair(w1, r, lane);
             const float u0 = wts[r], u1 = wts[kMaxWW + r];
             a0.x = fmaf(u0, x0.x, a0.x); a0.y = fmaf(u0, x0.y, a0.y);
             a1.x = fmaf(u1, x1.x, a1.x); a1.y = fmaf(u1, x1.y, a1.y);
         }
-        reinterpret_cast<float2*>(mixed)[lane] = make_float2(a0.x + b0, a0.y + b0);
-        reinterpret_cast<float2*>(mixed + kC)[lane] = make_float2(a1.x + b1, a1.y + b1);
+        reinterpret_cast<float2*>(mixed)[lane] = make_float2((a0.x + c0e.x) + b0, (a0.y + c0e.y) + b0);
+        reinterpret_cast<float2*>(mixed + kC)[lane] = make_float2((a1.x + c1e.x) + b1, (a1.y + c1e.y) + b1);
         __syncwarp();
 
         // ---- phase B: one window cell per lane (cells lane and lane + 32)
         float s0a = 0.f, s0b = 0.f, s1a = 0.f, s1b = 0.f;
         if (has_a) { s0a = row_dot(w1, mixed, ra); s1a = row_dot(w0, mixed + kC, ra); }
         if (has_b) { s0b = row_dot(w1, mixed, rb); s1b = row_dot(w0, mixed + kC, rb); }
-        float ex0, ey0, sd0, ex1, ey1, sd1;
-        heat_stats(has_a ? s0a : -INFINITY, s0b, has_b, ga_x, ga_y, gb_x, gb_y, temp, ex0, ey0, sd0);
-        heat_stats(has_a ? s1a : -INFINITY, s1b, has_b, ga_x, ga_y, gb_x, gb_y, temp, ex1, ey1, sd1);
+        HeatOut h0, h1;
+        heat_stats2(s0a, s0b, s1a, s1b, has_a, has_b, ga_x, ga_y, gb_x, gb_y, temp, h0, h1);
+        const float ex0 = h0.ex, ey0 = h0.ey, sd0 = h0.sd, ex1 = h1.ex, ey1 = h1.ey, sd1 = h1.sd;
         if (lane == 0) {
-            const float2 c0 = reinterpret_cast<const float2*>(mkpts0_c)[m];
-            const float2 c1 = reinterpret_cast<const float2*>(mkpts1_c)[m];
             out0[3 * m + 0] = c0.x + (ex0 * half * scale + half);
             out0[3 * m + 1] = c0.y + (ey0 * half * scale + half);
             out0[3 * m + 2] = sd0;
@@ -186,13 +240,14 @@ __global__ void __launch_bounds__(kWarps * 32) fine_match_kernel(
     }
 }
 
-template <typename T, int kWarps>
+template <typename T, int kWarps, int kStages>
 cudaError_t launch(const void* win0, const void* win1, const float* mk0, const float* mk1, const float* w0,
                    const float* b0, const float* w1, const float* b1, const int* count, int capacity, int WW,
                    float scale, float* out0, float* out1, int num_sms, cudaStream_t st) {
-    const size_t smem = static_cast<size_t>(kWarps) * 4 * WW * kC * sizeof(T) + sizeof(float) * (kWarps * 2 * kC + 2 * kMaxWW) +
-                        sizeof(uint64_t) * kWarps * 2;
-    auto kern = fine_match_kernel<T, kWarps>;
+    const size_t smem = static_cast<size_t>(kWarps) * kStages * 2 * WW * kC * sizeof(T) +
+                        sizeof(float) * (kWarps * 2 * kC + 2 * kMaxWW) + sizeof(uint64_t) * kWarps * kStages;
+    if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
+    auto kern = fine_match_kernel<T, kWarps, kStages>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return e;
     int W = 1;
@@ -256,10 +311,20 @@ cudaError_t launch_fine_match(const void* win0, const void* win1, int dtype, con
                               const float* w0, const float* b0, const float* w1, const float* b1, const int* count,
                               int capacity, int WW, float scale, float* out0, float* out1, int num_sms,
                               cudaStream_t st) {
-    if (dtype == FM_DTYPE_BF16)
-        return launch<__nv_bfloat16, 8>(win0, win1, mk0, mk1, w0, b0, w1, b1, count, capacity, WW, scale, out0, out1,
-                                        num_sms, st);
-    return launch<float, 4>(win0, win1, mk0, mk1, w0, b0, w1, b1, count, capacity, WW, scale, out0, out1, num_sms, st);
+    // FM_FINE_CFG = <warps><stages> picks another ring shape (tuning hook, fp32 windows only)
+    static const int cfg = [] { const char* e = getenv("FM_FINE_CFG"); return e ? atoi(e) : 0; }();
+#define FM_FINE_ARGS win0, win1, mk0, mk1, w0, b0, w1, b1, count, capacity, WW, scale, out0, out1, num_sms, st
+    if (dtype == FM_DTYPE_BF16) return launch<__nv_bfloat16, 8, 2>(FM_FINE_ARGS);
+    switch (cfg) {
+        case 81: return launch<float, 8, 1>(FM_FINE_ARGS);
+        case 33: return launch<float, 3, 3>(FM_FINE_ARGS);
+        case 24: return launch<float, 2, 4>(FM_FINE_ARGS);
+        case 22: return launch<float, 2, 2>(FM_FINE_ARGS);
+        case 41: return launch<float, 4, 1>(FM_FINE_ARGS);
+        case 42: return launch<float, 4, 2>(FM_FINE_ARGS);
+        default: return launch<float, 8, 1>(FM_FINE_ARGS);   // measured best on B200 (r01 sweep)
+    }
+#undef FM_FINE_ARGS
 }
 
 }  // namespace fm

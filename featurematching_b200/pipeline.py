@@ -122,35 +122,80 @@ class MatchHead:
         return st[_lib.ST_COUNT]
 
     # ---------------------------------------------------------------- host-buffer entry point
-    def _staging(self, name, t):
-        buf = self._host.get(name)
-        if buf is None or buf.shape != t.shape or buf.dtype != t.dtype:
-            buf = torch.empty_like(t, device=self.device)   # keeps the strides (channels-last maps)
-            self._host[name] = buf
-        return buf
+    def _host_state(self, shapes, chunk, capacity):
+        """Double-buffered device staging for `chunk` pairs, pinned landing buffers for the
+        records / status words of every chunk, the copy stream and its events."""
+        key = (tuple(shapes), chunk, capacity)
+        st = self._host.get("state")
+        if st is not None and st["key"] == key:
+            return st
+        dev = self.device
+        st = {"key": key, "copy_stream": torch.cuda.Stream(device=dev), "stage": [], "free": [], "ready": []}
+        for _ in range(2):
+            bufs = []
+            for shape, dtype, strides in shapes:
+                t = torch.empty_strided((chunk,) + tuple(shape[1:]), strides, dtype=dtype, device=dev)
+                bufs.append(t)
+            st["stage"].append(bufs)
+            st["free"].append(torch.cuda.Event())
+            st["ready"].append(torch.cuda.Event())
+        self._host["state"] = st
+        return st
 
-    def match_host(self, feat_c0, feat_c1, feat_f0, feat_f1, hw0_i, hw0_c, hw1_c, hw0_f, pair_offset=0):
-        """End-to-end call on HOST tensors (pinned for full copy bandwidth): copies the features
-        to the device, runs the head, and returns the match records as a numpy structured array
-        (RECORD_DTYPE).  Also returns the bytes moved each way."""
-        dev_in = []
+    def match_host(self, feat_c0, feat_c1, feat_f0, feat_f1, hw0_i, hw0_c, hw1_c, hw0_f, pair_offset=0,
+                   chunks=4):
+        """End-to-end call on HOST tensors (pinned for full copy bandwidth).  The batch is cut into
+        `chunks` groups of pairs; group k + 1 crosses PCIe on a copy stream while group k runs the
+        head, and each group's packed records (padded to capacity, the count is in the header
+        record) and status word come back with asynchronous copies.  One host synchronisation per
+        call.  Returns (records as a numpy structured array (RECORD_DTYPE), bytes host->device,
+        bytes device->host)."""
+        B = feat_c0.shape[0]
+        nch = max(1, min(int(chunks), B))
+        chunk = (B + nch - 1) // nch
+        nch = (B + chunk - 1) // chunk
+        cm = self.coarse_matching
+        capacity = self.default_capacity(chunk, hw0_c, hw1_c, cm.border_rm)
+        ins = (feat_c0, feat_c1, feat_f0, feat_f1)
+        st = self._host_state([(t.shape, t.dtype, t.stride()) for t in ins], chunk, capacity)
+        rec_bytes = (capacity + 1) * _lib.RECORD_BYTES
+        land = self._host.get("land")
+        if land is None or land[0].shape != (nch, rec_bytes):
+            land = (torch.empty(nch, rec_bytes, dtype=torch.uint8).pin_memory(),
+                    torch.empty(nch, _lib.STATUS_WORDS, dtype=torch.int32).pin_memory())
+            self._host["land"] = land
+        rec_host, status_host = land
+        cur = torch.cuda.current_stream(self.device)
+        cs = st["copy_stream"]
         h2d = 0
-        for name, t in (("c0", feat_c0), ("c1", feat_c1), ("f0", feat_f0), ("f1", feat_f1)):
-            d = self._staging(name, t)
-            d.copy_(t, non_blocking=True)
-            h2d += t.numel() * t.element_size()
-            dev_in.append(d)
-        r = self.run(*dev_in, hw0_i, hw0_c, hw1_c, hw0_f, pair_offset=pair_offset)
-        M = self.check_status(r)
-        nbytes = (M + 1) * _lib.RECORD_BYTES
-        out = self._host.get("rec")
-        if out is None or out.numel() < nbytes:
-            out = torch.empty(max(nbytes, (r.capacity + 1) * _lib.RECORD_BYTES), dtype=torch.uint8).pin_memory()
-            self._host["rec"] = out
-        out[:nbytes].copy_(r.records[:nbytes], non_blocking=True)
-        torch.cuda.current_stream(self.device).synchronize()
-        rec = out[:nbytes].numpy().view(RECORD_DTYPE)
-        return rec[1:], h2d, nbytes + _lib.STATUS_WORDS * 4
+        cs.wait_stream(cur)   # staging buffers may still be read by the previous call's kernels
+        for k in range(nch):
+            lo, hi = k * chunk, min((k + 1) * chunk, B)
+            slot = k & 1
+            with torch.cuda.stream(cs):
+                if k >= 2:
+                    cs.wait_event(st["free"][slot])
+                for d, t in zip(st["stage"][slot], ins):
+                    d[:hi - lo].copy_(t[lo:hi], non_blocking=True)
+                    h2d += (hi - lo) * t[0].numel() * t.element_size()
+                st["ready"][slot].record(cs)
+            cur.wait_event(st["ready"][slot])
+            dev_in = [d[:hi - lo] for d in st["stage"][slot]]
+            r = self.run(*dev_in, hw0_i, hw0_c, hw1_c, hw0_f, capacity=capacity, pair_offset=pair_offset + lo)
+            rec_host[k].copy_(r.records[:rec_bytes], non_blocking=True)
+            status_host[k].copy_(r.coarse.status, non_blocking=True)
+            st["free"][slot].record(cur)
+        cur.synchronize()
+        parts = []
+        for k in range(nch):
+            stw = status_host[k].tolist()
+            if stw[_lib.ST_FLAGS]:
+                raise _lib.FmError(f"coarse status flags {stw[_lib.ST_FLAGS]:#x} in chunk {k} (cand overflow=1, "
+                                   f"output overflow=2, tie overflow=4, range=8); status={stw}")
+            a = rec_host[k].numpy().view(RECORD_DTYPE)
+            parts.append(a[1:1 + stw[_lib.ST_COUNT]])
+        rec = np.concatenate(parts) if len(parts) > 1 else parts[0].copy()
+        return rec, h2d, nch * (rec_bytes + _lib.STATUS_WORDS * 4)
 
 
 def unpack_records(buf, capacity, world):
