@@ -13,6 +13,7 @@ FM_OK = 0
 DTYPE_BF16, DTYPE_F32 = 0, 1
 STATUS_WORDS = 8
 RECORD_BYTES = 40
+MAX_CHUNKS = 64
 ST_COUNT, ST_FLAGS, ST_MAX_CAND, ST_LOST, ST_CAND_TOTAL = 0, 1, 2, 3, 4
 FLAG_CAND_OVERFLOW, FLAG_OUT_OVERFLOW, FLAG_TIE_OVERFLOW, FLAG_RANGE = 1, 2, 4, 8
 
@@ -37,6 +38,7 @@ SIGNATURES = {
     "fm_fine_gather": (_I, [_P, _P, _P, _P, _I, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I,
                             _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P, _Z, _P]),
     "fm_pack_matches": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P]),
+    "fm_pack_matches_append": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _I, _I, _P, _P]),
     "fm_profile_enable": (_I, [_I]),
     "fm_profile_collect": (_I, [_c.POINTER(_c.c_float), _c.POINTER(_c.c_int)]),
     "fm_fine_match": (_I, [_P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _P, _P]),

@@ -276,12 +276,24 @@ __global__ void __launch_bounds__(256) pack_matches_kernel(const int64_t* __rest
                                                            const float* __restrict__ mk0,
                                                            const float* __restrict__ mk1,
                                                            const int* __restrict__ count, int capacity,
-                                                           int pair_offset, MatchRecord* __restrict__ rec) {
-    const int M = min(*count, capacity);
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        MatchRecord h = {M, pair_offset, 0, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        rec[0] = h;
+                                                           int pair_offset, MatchRecord* __restrict__ rec,
+                                                           int* __restrict__ chunk_counts, int chunk_index,
+                                                           int total_capacity) {
+    int M = min(*count, capacity);
+    // append mode: this call's records follow those of the earlier chunks of the same batch,
+    // whose counts the earlier pack kernels (same stream) left in chunk_counts[0 .. chunk_index)
+    int base = 0;
+    if (chunk_counts) {
+        for (int k = 0; k < chunk_index; ++k) base += chunk_counts[k];
+        M = max(0, min(M, total_capacity - base));
     }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        MatchRecord h = {base + M, chunk_counts ? rec[0].i : pair_offset, 0, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (chunk_counts && chunk_index == 0) h.i = pair_offset;
+        rec[0] = h;
+        if (chunk_counts) chunk_counts[chunk_index] = M;
+    }
+    rec += base;
     for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < M; m += gridDim.x * blockDim.x) {
         MatchRecord r;
         r.pair = static_cast<int>(b_ids[m]) + pair_offset;
@@ -298,12 +310,14 @@ __global__ void __launch_bounds__(256) pack_matches_kernel(const int64_t* __rest
 
 cudaError_t launch_pack_matches(const int64_t* b_ids, const int64_t* i_ids, const int64_t* j_ids, const float* mconf,
                                 const float* mk0, const float* mk1, const int* count, int capacity, int pair_offset,
-                                void* records, int num_sms, cudaStream_t st) {
+                                void* records, int* chunk_counts, int chunk_index, int total_capacity, int num_sms,
+                                cudaStream_t st) {
     int grid = (capacity + 255) / 256;
     if (grid > num_sms * 8) grid = num_sms * 8;
     if (grid < 1) grid = 1;
     pack_matches_kernel<<<grid, 256, 0, st>>>(b_ids, i_ids, j_ids, mconf, mk0, mk1, count, capacity, pair_offset,
-                                              static_cast<MatchRecord*>(records));
+                                              static_cast<MatchRecord*>(records), chunk_counts, chunk_index,
+                                              total_capacity);
     return cudaGetLastError();
 }
 

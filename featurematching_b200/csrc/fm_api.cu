@@ -166,7 +166,8 @@ cudaError_t launch_fine_gather_tc(const void* ff0, const void* ff1, const void* 
 cudaError_t launch_to_nhwc(const void* src, int src_dtype, int B, int C, int H, int W, void* dst, cudaStream_t st);
 cudaError_t launch_pack_matches(const int64_t* b_ids, const int64_t* i_ids, const int64_t* j_ids, const float* mconf,
                                 const float* mk0, const float* mk1, const int* count, int capacity, int pair_offset,
-                                void* records, int num_sms, cudaStream_t st);
+                                void* records, int* chunk_counts, int chunk_index, int total_capacity, int num_sms,
+                                cudaStream_t st);
 cudaError_t launch_fine_match(const void* win0, const void* win1, int dtype, const float* mk0, const float* mk1,
                               const float* w0, const float* b0, const float* w1, const float* b1, const int* count,
                               int capacity, int WW, float scale, float* out0, float* out1, int num_sms,
@@ -438,7 +439,25 @@ int fm_pack_matches(const int64_t* b_ids, const int64_t* i_ids, const int64_t* j
     const int sms = sm_count();
     if (sms <= 0) { set_error("no CUDA device available (this library has no CPU path)"); return FM_ERR_CUDA; }
     cudaError_t e = launch_pack_matches(b_ids, i_ids, j_ids, mconf, mkpts0_f, mkpts1_f, count, capacity, pair_offset,
-                                        records, sms, static_cast<cudaStream_t>(stream));
+                                        records, nullptr, 0, 0, sms, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "pack_matches launch");
+    return FM_OK;
+}
+
+int fm_pack_matches_append(const int64_t* b_ids, const int64_t* i_ids, const int64_t* j_ids, const float* mconf,
+                           const float* mkpts0_f, const float* mkpts1_f, const int32_t* count, int capacity,
+                           int pair_offset, int32_t* chunk_counts, int chunk_index, int total_capacity, void* records,
+                           void* stream) {
+    if (!b_ids || !i_ids || !j_ids || !mconf || !mkpts0_f || !mkpts1_f || !count || !records || !chunk_counts ||
+        capacity < 0 || chunk_index < 0 || chunk_index >= FM_MAX_CHUNKS || total_capacity < 0) {
+        set_error("bad argument to fm_pack_matches_append");
+        return FM_ERR_BAD_ARG;
+    }
+    const int sms = sm_count();
+    if (sms <= 0) { set_error("no CUDA device available (this library has no CPU path)"); return FM_ERR_CUDA; }
+    cudaError_t e = launch_pack_matches(b_ids, i_ids, j_ids, mconf, mkpts0_f, mkpts1_f, count, capacity, pair_offset,
+                                        records, chunk_counts, chunk_index, total_capacity, sms,
+                                        static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return cuda_fail(e, "pack_matches launch");
     return FM_OK;
 }

@@ -79,7 +79,7 @@ class MatchHead:
         return r
 
     def run(self, feat_c0, feat_c1, feat_f0, feat_f1, hw0_i, hw0_c, hw1_c, hw0_f, capacity=None,
-            pair_offset=0, pack=True):
+            pair_offset=0, pack=True, append=None):
         """Enqueues the whole head on the current stream; no host synchronisation.
         feat_c*: [B, N, C] bf16/fp32; feat_f*: [B, Cf, Hf, Wf] (channels-last bf16 is read in place)."""
         B = feat_c0.shape[0]
@@ -102,7 +102,18 @@ class MatchHead:
             scale = float(hw0_i[0]) / float(hw0_f[0])
             fin.refine(w0, w1, c.mkpts0_c, c.mkpts1_c, scale, count=count,
                        out=(r.mkpts0_f, r.mkpts1_f))
-            if pack:
+            if append is not None:
+                # chunked batch: records go behind those of the earlier chunks (fm_pack_matches_append)
+                counts, index, total_capacity, records = append
+                lib = _lib.load()
+                with torch.cuda.device(self.device):
+                    rc = lib.fm_pack_matches_append(_lib.ptr(c.b_ids), _lib.ptr(c.i_ids), _lib.ptr(c.j_ids),
+                                                    _lib.ptr(c.mconf), _lib.ptr(r.mkpts0_f), _lib.ptr(r.mkpts1_f),
+                                                    _lib.ptr(count), r.capacity, int(pair_offset), _lib.ptr(counts),
+                                                    int(index), int(total_capacity), _lib.ptr(records),
+                                                    _lib.stream_ptr(self.device))
+                _lib.check(rc, "fm_pack_matches_append")
+            elif pack:
                 lib = _lib.load()
                 with torch.cuda.device(self.device):
                     rc = lib.fm_pack_matches(_lib.ptr(c.b_ids), _lib.ptr(c.i_ids), _lib.ptr(c.j_ids),
@@ -143,28 +154,34 @@ class MatchHead:
         return st
 
     def match_host(self, feat_c0, feat_c1, feat_f0, feat_f1, hw0_i, hw0_c, hw1_c, hw0_f, pair_offset=0,
-                   chunks=4):
+                   chunks=8):
         """End-to-end call on HOST tensors (pinned for full copy bandwidth).  The batch is cut into
         `chunks` groups of pairs; group k + 1 crosses PCIe on a copy stream while group k runs the
-        head, and each group's packed records (padded to capacity, the count is in the header
-        record) and status word come back with asynchronous copies.  One host synchronisation per
-        call.  Returns (records as a numpy structured array (RECORD_DTYPE), bytes host->device,
-        bytes device->host)."""
+        head; the groups' packed records are appended on the device (fm_pack_matches_append) and
+        come back, with the status words, in asynchronous copies.  One host synchronisation per
+        call.  Returns (records as a numpy structured array (RECORD_DTYPE) that VIEWS a pinned
+        landing buffer reused by the next call -- copy it to keep it --, bytes host->device, bytes
+        device->host)."""
+        import time
+        t_start = time.perf_counter()
         B = feat_c0.shape[0]
-        nch = max(1, min(int(chunks), B))
+        nch = max(1, min(int(chunks), B, _lib.MAX_CHUNKS))
         chunk = (B + nch - 1) // nch
         nch = (B + chunk - 1) // chunk
         cm = self.coarse_matching
         capacity = self.default_capacity(chunk, hw0_c, hw1_c, cm.border_rm)
         ins = (feat_c0, feat_c1, feat_f0, feat_f1)
         st = self._host_state([(t.shape, t.dtype, t.stride()) for t in ins], chunk, capacity)
-        rec_bytes = (capacity + 1) * _lib.RECORD_BYTES
+        total_capacity = nch * capacity
+        rec_bytes = (total_capacity + 1) * _lib.RECORD_BYTES
         land = self._host.get("land")
-        if land is None or land[0].shape != (nch, rec_bytes):
-            land = (torch.empty(nch, rec_bytes, dtype=torch.uint8).pin_memory(),
-                    torch.empty(nch, _lib.STATUS_WORDS, dtype=torch.int32).pin_memory())
+        if land is None or land[0].numel() != rec_bytes or land[1].shape[0] != nch:
+            land = (torch.empty(rec_bytes, dtype=torch.uint8).pin_memory(),
+                    torch.empty(nch, _lib.STATUS_WORDS, dtype=torch.int32).pin_memory(),
+                    torch.empty(rec_bytes, dtype=torch.uint8, device=self.device),
+                    torch.zeros(_lib.MAX_CHUNKS, dtype=torch.int32, device=self.device))
             self._host["land"] = land
-        rec_host, status_host = land
+        rec_host, status_host, rec_dev, counts_dev = land
         cur = torch.cuda.current_stream(self.device)
         cs = st["copy_stream"]
         h2d = 0
@@ -181,21 +198,23 @@ class MatchHead:
                 st["ready"][slot].record(cs)
             cur.wait_event(st["ready"][slot])
             dev_in = [d[:hi - lo] for d in st["stage"][slot]]
-            r = self.run(*dev_in, hw0_i, hw0_c, hw1_c, hw0_f, capacity=capacity, pair_offset=pair_offset + lo)
-            rec_host[k].copy_(r.records[:rec_bytes], non_blocking=True)
+            r = self.run(*dev_in, hw0_i, hw0_c, hw1_c, hw0_f, capacity=capacity, pair_offset=pair_offset + lo,
+                         pack=False, append=(counts_dev, k, total_capacity, rec_dev))
             status_host[k].copy_(r.coarse.status, non_blocking=True)
             st["free"][slot].record(cur)
+        rec_host.copy_(rec_dev, non_blocking=True)
+        t_enq = time.perf_counter()
         cur.synchronize()
-        parts = []
-        for k in range(nch):
-            stw = status_host[k].tolist()
+        t_sync = time.perf_counter()
+        for k, stw in enumerate(status_host.tolist()):
             if stw[_lib.ST_FLAGS]:
                 raise _lib.FmError(f"coarse status flags {stw[_lib.ST_FLAGS]:#x} in chunk {k} (cand overflow=1, "
                                    f"output overflow=2, tie overflow=4, range=8); status={stw}")
-            a = rec_host[k].numpy().view(RECORD_DTYPE)
-            parts.append(a[1:1 + stw[_lib.ST_COUNT]])
-        rec = np.concatenate(parts) if len(parts) > 1 else parts[0].copy()
-        return rec, h2d, nch * (rec_bytes + _lib.STATUS_WORDS * 4)
+        a = rec_host.numpy().view(RECORD_DTYPE)
+        rec = a[1:1 + int(a[0]["pair"])]   # a view of the pinned landing buffer: valid until the next call
+        # host-side split of the call (ms): enqueue, wait for the device, unpack
+        self.last_timing = ((t_enq - t_start) * 1e3, (t_sync - t_enq) * 1e3, (time.perf_counter() - t_sync) * 1e3)
+        return rec, h2d, rec_bytes + nch * _lib.STATUS_WORDS * 4
 
 
 def unpack_records(buf, capacity, world):

@@ -158,6 +158,18 @@ FM_API int fm_pack_matches(const int64_t* b_ids, const int64_t* i_ids, const int
                            const int32_t* count, int capacity, int pair_offset, void* records,
                            void* stream);
 
+/* Append form for a batch processed in chunks of pairs on one stream: chunk `chunk_index`
+ * (0 .. FM_MAX_CHUNKS-1, in call order) writes its records behind those of the earlier chunks and
+ * leaves its count in chunk_counts[chunk_index] (device int32[FM_MAX_CHUNKS]); the header record
+ * carries the running total and the pair_offset of chunk 0.  records: (total_capacity + 1) * 40
+ * bytes.  One device->host copy of `records` then returns the whole batch. */
+#define FM_MAX_CHUNKS 64
+FM_API int fm_pack_matches_append(const int64_t* b_ids, const int64_t* i_ids, const int64_t* j_ids,
+                                  const float* mconf, const float* mkpts0_f, const float* mkpts1_f,
+                                  const int32_t* count, int capacity, int pair_offset,
+                                  int32_t* chunk_counts, int chunk_index, int total_capacity,
+                                  void* records, void* stream);
+
 /* ---------------------------------------------------------------- test / profiling hooks
  * Same contract as fm_coarse_match, but the score statistics come from a plain SIMT kernel
  * instead of the tcgen05 kernel.  Exists so tests can tell a tensor-core plumbing bug from a

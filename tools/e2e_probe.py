@@ -54,4 +54,11 @@ head = pipeline.MatchHead(cfg, dev)
 head.load_params(synth.hot_path_params(seed=99))
 for ch in (1, 2, 4, 8, 16):
     ms = timed(lambda: head.match_host(*host, hw_i, hw_c, hw_c, hw_f, chunks=ch))
-    print(f"match_host chunks={ch}: {ms:.2f} ms/step = {B / ms * 1e3:.0f} pairs/s")
+    print(f"match_host chunks={ch}: {ms:.2f} ms/step = {B / ms * 1e3:.0f} pairs/s; enqueue/wait/unpack ms = "
+          + "/".join(f"{x:.2f}" for x in head.last_timing))
+# device-only time of the same head on resident inputs
+r = head.run(fc0, fc1, ff0, ff1, hw_i, hw_c, hw_c, hw_f)
+ms = timed(lambda: head.run(fc0, fc1, ff0, ff1, hw_i, hw_c, hw_c, hw_f), n=20)
+print(f"head.run resident B=32: {ms:.2f} ms")
+ms = timed(lambda: [head.run(fc0[8 * k:8 * k + 8], fc1[8 * k:8 * k + 8], ff0[8 * k:8 * k + 8], ff1[8 * k:8 * k + 8], hw_i, hw_c, hw_c, hw_f) for k in range(4)], n=20)
+print(f"head.run resident 4 x B=8: {ms:.2f} ms")
