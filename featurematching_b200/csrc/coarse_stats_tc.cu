@@ -219,11 +219,15 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
 #pragma unroll
             for (int k = 0; k < 64; ++k) colacc[k] = 0ull;
 
+            // token norm of this thread's row, fetched one tile ahead (N0pad rows exist)
+            const float* norm_b = p.norm0 + static_cast<size_t>(b) * d.N0pad + q * 32 + lane;
+            float n0_next = __ldg(norm_b + mt0 * kTileM);
             for (int mt = mt0; mt < mt1; ++mt, ++tile_it) {
                 const uint32_t buf = tile_it & 1, tph = (tile_it >> 1) & 1;
                 const int row = mt * kTileM + q * 32 + lane;
                 const bool rvalid = row < d.N0;
-                const float n0 = rvalid ? __ldg(p.norm0 + static_cast<size_t>(b) * d.N0pad + row) : 0.f;
+                const float n0 = rvalid ? n0_next : 0.f;
+                if (mt + 1 < mt1) n0_next = __ldg(norm_b + (mt + 1) * kTileM);
                 const float ci = score_bound2(n0, maxn1, p.a2) - kHead2;
                 const float bias = rvalid ? -ci : -INFINITY;          // invalid row -> p = 0
                 const float wi = rvalid ? ex2_approx(ci - cref) : 0.f;  // <= 1

@@ -278,8 +278,8 @@ window_merge_kernel(const __grid_constant__ CUtensorMap tmap_f0, const __grid_co
                 for (int w = 0; w < nvalid; ++w) {
                     const int m = m0 + w;
                     const int b = static_cast<int>(__ldg(p.b_ids + m));
-                    const int cell = static_cast<int>(__ldg(p.ids[side] + m));
-                    const int cr = cell / p.wc[side], cc = cell - cr * p.wc[side];
+                    const int cell = static_cast<int>(__ldg((side ? p.ids[1] : p.ids[0]) + m));
+                    const int cr = cell / (side ? p.wc[1] : p.wc[0]), cc = cell - cr * (side ? p.wc[1] : p.wc[0]);
                     tma_load_4d(smem_a + static_cast<size_t>(s) * kStageBytes + w * kWinRows * 128,
                                 side ? &tmap_f1 : &tmap_f0, &ctl->a_full[s], 0, cc * p.stride - p.pad,
                                 cr * p.stride - p.pad, b);
@@ -316,18 +316,35 @@ window_merge_kernel(const __grid_constant__ CUtensorMap tmap_f0, const __grid_co
         const int w = q >> 1;                       // window slot of this thread's row
         const int ww = (q & 1) * 32 + lane;         // window cell
         uint8_t* stg = smem_o + static_cast<size_t>(g) * 2 * kHalves * kStgBytes + static_cast<size_t>(w) * kHalves * kStgBytes;
+        // match / cell ids of this warpgroup's NEXT tile are fetched one tile ahead and the 64
+        // context values of the current tile before the accumulator wait, so neither global
+        // latency sits between the TMEM read and the stores
+        auto tile_ids = [&](int t, int& b, int& cell) {
+            const int side = t & 1, m = (t >> 1) * 2 + w;
+            b = 0; cell = 0;
+            if (t < tiles && m < M && ww < p.WW) {
+                b = static_cast<int>(__ldg(p.b_ids + m));
+                cell = static_cast<int>(__ldg((side ? p.ids[1] : p.ids[0]) + m));
+            }
+        };
+        int nb, ncell;
+        tile_ids(blockIdx.x + g * gridDim.x, nb, ncell);
         uint32_t it = 0;
         for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++it) {
             if ((it & 1) != static_cast<uint32_t>(g)) continue;
             const int side = t & 1, m0 = (t >> 1) * 2;
             const int m = m0 + w;
             const bool valid = m < M && ww < p.WW;
-            const float4* cv = nullptr;
+            float4 cx[16];
             if (valid) {
-                const int b = static_cast<int>(__ldg(p.b_ids + m));
-                const int cell = static_cast<int>(__ldg(p.ids[side] + m));
-                cv = reinterpret_cast<const float4*>(p.ctx[side] + (static_cast<size_t>(b) * p.N[side] + cell) * kCf);
+                const float4* cv = reinterpret_cast<const float4*>((side ? p.ctx[1] : p.ctx[0]) + (static_cast<size_t>(nb) * (side ? p.N[1] : p.N[0]) + ncell) * kCf);
+#pragma unroll
+                for (int c = 0; c < 16; ++c) cx[c] = __ldg(cv + c);
+            } else {
+#pragma unroll
+                for (int c = 0; c < 16; ++c) cx[c] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
+            tile_ids(t + 2 * gridDim.x, nb, ncell);
             mbar_wait(&ctl->t_full[g], (it >> 1) & 1);
             tc_fence_after();
             uint32_t lo[32], hi[32];
@@ -345,14 +362,14 @@ window_merge_kernel(const __grid_constant__ CUtensorMap tmap_f0, const __grid_co
                 if constexpr (kHalves == 2) {
 #pragma unroll
                     for (int c = 0; c < 8; ++c) {
-                        const float4 a = __ldg(cv + c);
+                        const float4 a = cx[c];
                         *reinterpret_cast<float4*>(rowp + ((c ^ sw) << 4)) =
                             make_float4(__uint_as_float(lo[4 * c]) + a.x, __uint_as_float(lo[4 * c + 1]) + a.y,
                                         __uint_as_float(lo[4 * c + 2]) + a.z, __uint_as_float(lo[4 * c + 3]) + a.w);
                     }
 #pragma unroll
                     for (int c = 0; c < 8; ++c) {
-                        const float4 a = __ldg(cv + 8 + c);
+                        const float4 a = cx[8 + c];
                         *reinterpret_cast<float4*>(rowp + kStgBytes + ((c ^ sw) << 4)) =
                             make_float4(__uint_as_float(hi[4 * c]) + a.x, __uint_as_float(hi[4 * c + 1]) + a.y,
                                         __uint_as_float(hi[4 * c + 2]) + a.z, __uint_as_float(hi[4 * c + 3]) + a.w);
@@ -361,7 +378,7 @@ window_merge_kernel(const __grid_constant__ CUtensorMap tmap_f0, const __grid_co
 #pragma unroll
                     for (int c = 0; c < 8; ++c) {   // 8 channels = 16 B of bf16 per chunk
                         const uint32_t* src = c < 4 ? lo + 8 * c : hi + 8 * (c - 4);
-                        const float4 a0 = __ldg(cv + 2 * c), a1 = __ldg(cv + 2 * c + 1);
+                        const float4 a0 = cx[2 * c], a1 = cx[2 * c + 1];
                         __nv_bfloat162 v[4] = {
                             __floats2bfloat162_rn(__uint_as_float(src[0]) + a0.x, __uint_as_float(src[1]) + a0.y),
                             __floats2bfloat162_rn(__uint_as_float(src[2]) + a0.z, __uint_as_float(src[3]) + a0.w),
