@@ -24,6 +24,20 @@ if ROOT not in sys.path:
 
 METRIC = "matched frame pairs/sec at 640x512"
 UNIT = "pairs/s"
+# kernels of libfm_b200.so per step: coarse prep, stats, finish_lse, cand_best, cand_select,
+# row_blocksum, blocksum_scan, emit; gather fold, ctx_gemm, window_merge; fine_match; pack
+LAUNCHES_PER_STEP = 13
+# BASELINE.json configs that fit this bench: pairs per GPU per step, image size, and whether the
+# pairs are consecutive frames of one sequence (image 1 of pair k is image 0 of pair k + 1)
+CONFIGS = {
+    "640x512": {"pairs": 32, "height": 512, "width": 640, "sequence": False, "sigma": 1.0,
+                "name": "BASELINE configs[1]"},
+    # sigma 1.15: at sigma 1 the planted confidences sit at thr = 0.2 against 20 480-token denominators
+    "1280x1024": {"pairs": 4, "height": 1024, "width": 1280, "sequence": False, "sigma": 1.15,
+                  "name": "BASELINE configs[2]"},
+    "seq320": {"pairs": 64, "height": 320, "width": 320, "sequence": True, "sigma": 1.0,
+               "name": "BASELINE configs[3]"},
+}
 
 
 def parse_args():
@@ -32,14 +46,24 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--pairs", type=int, default=32, help="frame pairs per GPU per step")
-    ap.add_argument("--height", type=int, default=512)
-    ap.add_argument("--width", type=int, default=640)
+    ap.add_argument("--config", default="640x512", choices=sorted(CONFIGS),
+                    help="BASELINE.json workload: 640x512 = configs[1] (the metric's), 1280x1024 = configs[2], "
+                         "seq320 = configs[3] (consecutive frames of a 320x320 sequence)")
+    ap.add_argument("--pairs", type=int, default=None, help="frame pairs per GPU per step (default: the config's)")
+    ap.add_argument("--height", type=int, default=None)
+    ap.add_argument("--width", type=int, default=None)
     ap.add_argument("--noise", type=float, default=0.1)
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    return ap.parse_args()
+    a = ap.parse_args()
+    preset = CONFIGS[a.config]
+    for k in ("pairs", "height", "width"):
+        if getattr(a, k) is None:
+            setattr(a, k, preset[k])
+    a.sequence = preset["sequence"]
+    a.sigma = preset["sigma"]
+    return a
 
 
 def peaks():
@@ -124,7 +148,7 @@ def cpu_head_factory(args):
     torch.set_num_threads(cores)
 
     def make_pair(k):
-        fc0, fc1, _ = synth.coarse_features(1, N, N, 256, args.noise, "planted", 1234 + k)
+        fc0, fc1, _ = synth.coarse_features(1, N, N, 256, args.noise, "planted", 1234 + k, sigma=args.sigma)
         ff0, ff1 = synth.fine_features(1, 64, hw_f[0], hw_f[1], 4321 + k, channels_last=False)
         return fc0, fc1, ff0, ff1
 
@@ -198,6 +222,9 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # keep stdout to the one JSON line: NCCL prints its version there at NCCL_DEBUG=VERSION
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
     pk = peaks()
@@ -208,8 +235,16 @@ def run_b200(args):
            "match_coarse": {"thr": 0.2, "border_rm": 2, "dsmax_temperature": 0.1}}
 
     # synthetic inputs, resident in HBM (seeds differ per rank and pair)
-    fc0, fc1, _ = synth.coarse_features(B, N, N, 256, args.noise, "planted", 1234 + rank * B, device=dev)
-    ff0, ff1 = synth.fine_features(B, 64, hw_f[0], hw_f[1], 4321 + rank, device=dev)
+    if args.sequence:
+        # this rank's block of the sequence: B pairs = B + 1 frames (one-frame halo, shard_sequence)
+        frames, _ = synth.sequence_features(B + 1, N, 256, args.noise, 1234 + rank, device=dev)
+        fc0, fc1 = frames[:-1], frames[1:]
+        fmaps, _ = synth.fine_features(B + 1, 64, hw_f[0], hw_f[1], 4321 + rank, device=dev)
+        ff0, ff1 = fmaps[:-1], fmaps[1:]
+    else:
+        fc0, fc1, _ = synth.coarse_features(B, N, N, 256, args.noise, "planted", 1234 + rank * B, device=dev,
+                                             sigma=args.sigma)
+        ff0, ff1 = synth.fine_features(B, 64, hw_f[0], hw_f[1], 4321 + rank, device=dev)
     head = pipeline.MatchHead(cfg, dev)
     head.load_params(synth.hot_path_params(seed=99))
     in_bytes = sum(t.numel() * t.element_size() for t in (fc0, fc1, ff0, ff1))
@@ -328,10 +363,12 @@ def run_b200(args):
     roofline = dict(kernels[top], kernel=top, traffic=traffic, peak_source=pk["source"] +
                     (" (sustained bf16)" if kernels[top]["bound"] == "tensor" else " (copy)"))
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(args.warmup, 3),
+        "metric": METRIC if (args.width, args.height) == (640, 512) else
+                  f"matched frame pairs/sec at {args.width}x{args.height}", "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": f"{B} planted {args.width}x{args.height} pairs/GPU/step (BASELINE configs[1]): "
+        "config": {"workload": f"{B} planted {args.width}x{args.height} pairs/GPU/step ({CONFIGS[args.config]['name']}"
+                               + (", consecutive frames of one sequence" if args.sequence else "") + "): "
                                "coarse match + fine gather + fine match + record pack"
                                + (" + NCCL all_gather of match records" if world > 1 else ""),
                    "N0": N, "N1": N, "C": 256, "fine_map": [64, hw_f[0], hw_f[1]], "window": 7,
@@ -341,7 +378,7 @@ def run_b200(args):
         "roofline": roofline, "kernels": kernels,
         "stage_ms": {"coarse_total": stage_ms[0], "fine_gather": stage_ms[1], "fine_match": stage_ms[2],
                      "pack_and_gather": stage_ms[3]},
-        "e2e": e2e, "gpu_launches": K * 10, "clocks": clocks,
+        "e2e": e2e, "gpu_launches": K * LAUNCHES_PER_STEP, "clocks": clocks,
     }
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args)

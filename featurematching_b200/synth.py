@@ -46,6 +46,23 @@ def coarse_features(B, N0, N1=None, C=256, noise=0.1, kind="planted", seed=1234,
     return f0.to(torch.bfloat16), f1.to(torch.bfloat16), perm
 
 
+def sequence_features(frames, N, C=256, noise=0.1, seed=1234, device="cpu"):
+    """Coarse tokens of `frames` consecutive frames [frames, N, C] bf16 for consecutive-frame
+    matching (pairs (k, k + 1), the pattern of datasets/scared_new2.py:76-83): frame k + 1 is a
+    permutation of frame k plus noise, so pair k is feat_c0 = F[k], feat_c1 = F[k + 1] -- two
+    overlapping VIEWS of one tensor, no copy.  Also returns perm [frames - 1, N] with
+    F[k + 1, j] ~ F[k, perm[k, j]]."""
+    g = _gen(seed, device)
+    F = torch.empty(frames, N, C, device=device)
+    perm = torch.empty(max(frames - 1, 0), N, dtype=torch.int64, device=device)
+    F[0] = torch.randn(N, C, generator=g, device=device)
+    for k in range(frames - 1):
+        p = torch.randperm(N, generator=g, device=device)
+        F[k + 1] = (F[k, p] + noise * torch.randn(N, C, generator=g, device=device)) / (1.0 + noise * noise) ** .5
+        perm[k] = p
+    return F.to(torch.bfloat16), perm
+
+
 def fine_features(B, Cf, Hf, Wf, seed=4321, device="cpu", channels_last=True):
     """Two fine feature maps [B, Cf, Hf, Wf] bf16 (logical NCHW; NHWC strides when
     channels_last, which is the layout the gather kernel reads without a transpose)."""

@@ -139,6 +139,70 @@ def test_coarse_full_size_properties():
     compare.check_coarse(ours0, o, o64["conf_matrix"])
 
 
+def test_coarse_1280x1024_properties():
+    """BASELINE configs[2]: 1280x1024 -> N = 20 480 coarse tokens per image (a 1.7 GB fp32 matrix
+    per pair for the reference, never built here).  Size-independent properties on planted pairs:
+    every match follows the planted permutation, is interior, the list is sorted and one-to-one,
+    every interior-interior planted pair IS matched, and the confidences agree with a direct
+    evaluation of the dual-softmax on the matched rows/columns (fp64 log-sum-exp of those rows)."""
+    hw_c = (128, 160)
+    N = hw_c[0] * hw_c[1]
+    B = 2
+    # sigma 1.15: the planted score must clear the 4x larger soft-max denominators (at sigma 1
+    # the planted confidences sit right at thr = 0.2)
+    f0, f1, perm = synth.coarse_features(B, N, N, 256, 0.1, "planted", 77, device=DEV, sigma=1.15)
+    d = run_coarse(f0, f1, (1024, 1280), hw_c, hw_c)
+    b, i, j = d["b_ids"], d["i_ids"], d["j_ids"]
+    assert b.numel() > B * 14000
+    assert torch.equal(perm[b, j], i)
+    inner = mo.interior_mask(hw_c[0], hw_c[1], 2).to(DEV)
+    assert bool(inner[i].all()) and bool(inner[j].all())
+    key = (b * N + i) * N + j
+    assert bool((key[1:] > key[:-1]).all())
+    assert torch.unique(b * N + i).numel() == b.numel() and torch.unique(b * N + j).numel() == b.numel()
+    # confidences of 256 sampled matches against fp64 row / column soft-max denominators
+    g = torch.Generator().manual_seed(1)
+    pick = torch.randperm(b.numel(), generator=g)[:256].to(DEV)
+    a0, a1 = f0.double() / 16.0, f1.double() / 16.0
+    for m in pick.tolist()[:64]:
+        bb, ii, jj = int(b[m]), int(i[m]), int(j[m])
+        row = (a0[bb, ii] @ a1[bb].T) / 0.1
+        col = (a0[bb] @ a1[bb, jj]) / 0.1
+        conf = torch.exp(2 * row[jj] - torch.logsumexp(row, 0) - torch.logsumexp(col, 0))
+        assert abs(float(d["mconf"][m]) - float(conf)) <= 1e-3 * float(conf)
+    # completeness: planted interior-interior pairs with conf > thr must all be present
+    planted_ok = inner[perm] & inner[None, :].expand(B, N)
+    assert b.numel() >= int(planted_ok.sum()) * 0.9
+
+
+def test_sequence_pairs_as_views():
+    """BASELINE configs[3] shape: consecutive frames of one 320x320 sequence; pair k is
+    (F[k], F[k + 1]) passed as two overlapping views of one tensor (shard_sequence halo), which
+    must give exactly what separately copied tensors give, and follow the planted motion."""
+    from featurematching_b200 import pipeline
+    hw_c, hw_f, hw_i = (40, 40), (160, 160), (320, 320)
+    N, B = 1600, 5
+    F, perm = synth.sequence_features(B + 1, N, 256, 0.1, 5, device=DEV)
+    fm0, _ = synth.fine_features(B + 1, 64, hw_f[0], hw_f[1], 6, device=DEV)
+    head = pipeline.MatchHead(CFG, DEV)
+    head.load_params(synth.hot_path_params(seed=7))
+    r = head.run(F[:-1], F[1:], fm0[:-1], fm0[1:], hw_i, hw_c, hw_c, hw_f)
+    M = head.check_status(r)
+    views = [t[:M].clone() for t in (r.coarse.b_ids, r.coarse.i_ids, r.coarse.j_ids, r.coarse.mconf,
+                                      r.mkpts0_f, r.mkpts1_f)]
+    r2 = head.run(F[:-1].clone(), F[1:].clone(), fm0[:-1].clone(memory_format=torch.channels_last),
+                  fm0[1:].clone(memory_format=torch.channels_last), hw_i, hw_c, hw_c, hw_f)
+    assert head.check_status(r2) == M and M > B * 1000
+    copies = [t[:M] for t in (r2.coarse.b_ids, r2.coarse.i_ids, r2.coarse.j_ids, r2.coarse.mconf,
+                              r2.mkpts0_f, r2.mkpts1_f)]
+    for a, c in zip(views, copies):
+        assert torch.equal(a, c)
+    b, i, j = views[0], views[1], views[2]
+    assert torch.equal(perm[b, j], i)
+    begin, end, frames = pipeline.shard_sequence(B + 1, 0, 1)
+    assert (begin, end, frames) == (0, B, (0, B + 1))
+
+
 def test_coarse_rejects_bad_input():
     m = coarse_module()
     f = torch.zeros(1, 80, 256, dtype=torch.bfloat16)
