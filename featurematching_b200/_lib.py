@@ -41,6 +41,8 @@ SIGNATURES = {
     "fm_pack_matches_append": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _I, _I, _P, _P]),
     "fm_profile_enable": (_I, [_I]),
     "fm_profile_collect": (_I, [_c.POINTER(_c.c_float), _c.POINTER(_c.c_int)]),
+    "fm_fine_transformer_workspace_bytes": (_Z, [_I]),
+    "fm_fine_transformer": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _Z, _P]),
     "fm_fine_match": (_I, [_P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _P, _P]),
 }
 

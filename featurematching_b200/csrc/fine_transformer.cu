@@ -1,0 +1,502 @@
+// Fine LocalFeatureTransformer: the step between FinePreprocess and
+// FineMatching -- network/net.py:79-80 -> network/module/transformer.py:78-97, EncoderLayer
+// transformer.py:34-57, LinearAttention attentions.py:22-46 -- on [M, WW, 64] windows,
+// d_model 64, 8 heads, attention 'linear', layer_names any sequence of 'self' / 'cross'.
+//
+// One launch per encoder layer (the layer's weights, bf16 hi + lo parts, stay resident in shared
+// memory: 160 KB).  A tile is ONE match: TMEM lanes 0..WW-1 = its image-0 window, lanes
+// 64..64+WW-1 = its image-1 window, one lane per window cell.  Two tiles are in flight per SM
+// ("slots"); a slot has 8 epilogue warps (two warpgroups, each owning 32 of a row's 64 channels /
+// 4 of its 8 heads) and its own MMA-issuing warp, so the two slots overlap each other's tensor
+// and SIMT phases.
+//
+// Every GEMM is a tcgen05.mma with the ACTIVATIONS as the A operand IN TENSOR MEMORY (written by
+// the epilogue threads with tcgen05.st as packed bf16 pairs -- tools/probe_ts_mma.cu pins the
+// layout) and the weights as the K-major SW128 B operand in shared memory; fp32-grade products come
+// from the split a*b ~= ah*bh + ah*bl + al*bh (a = ah + al, bf16 parts; error 2^-17 relative).
+// Activations never touch shared memory; the only SIMT shared-memory traffic is the K^T V
+// reduction of the linear attention (cross-row) and the LayerNorm statistics exchange.
+//
+// TMEM columns of a slot (256):
+//   [  0,192) accumulators: Q|K|V (192) -> merge out (64) -> MLP hidden (128) -> MLP out (64)
+//   [128,192) after K/V are consumed: attention message, then LayerNorm-1 output (A operand:
+//             hi 32 columns + lo 32 columns), then the lo half of the hidden activations
+//   [192,256) X operand (hi 32 + lo 32); overwritten by the hi half of the hidden activations
+//             and rewritten with the updated x at the end of every pass
+#include <algorithm>
+
+#include "fm_common.cuh"
+#include "fm_ptx.cuh"
+
+namespace fm {
+
+namespace {
+
+constexpr int kC = 64;                 // d_model
+constexpr int kHeads = 8;
+constexpr int kMaxWW = 49;             // window cells per window (scratch sizing)
+constexpr int kTfThreads = 640;        // 16 epilogue warps + 2 MMA warps + loader + spare
+constexpr int kSlotThreads = 256;
+constexpr int kSlotCols = 256;
+
+// ---- per-layer weight blob: B operands (K-major, 128-byte swizzle, [term: hi, lo]) + LayerNorm
+constexpr int kOffQkv = 0;             // [2][192 rows x 128 B]      rows: q 0..63, k 64..127, v 128..191
+constexpr int kOffMerge = 49152;       // [2][64 x 128 B]
+constexpr int kOffMlp0 = 65536;        // [2][2 K chunks][128 x 128 B]
+constexpr int kOffMlp2 = 131072;       // [2][2 K chunks][64 x 128 B]
+constexpr int kOffLn = 163840;         // norm1.weight, norm1.bias, norm2.weight, norm2.bias: 4 x 64 fp32
+constexpr int kBlobBytes = 164864;
+constexpr int kScratchBytes = 2 * kMaxWW * 512;   // K | V fp32 of both windows, one 512-byte row per cell
+
+struct TfLayerParams {
+    const float* q; const float* k; const float* v; const float* merge;
+    const float* mlp0; const float* mlp2;
+    const float* n1w; const float* n1b; const float* n2w; const float* n2b;
+};
+
+__device__ __forceinline__ void put_split(uint8_t* tile_hi, uint8_t* tile_lo, int n, int kk, float w) {
+    const __nv_bfloat16 h = __float2bfloat16_rn(w);
+    const __nv_bfloat16 l = __float2bfloat16_rn(w - __bfloat162float(h));
+    const int off = n * 128 + ((((kk >> 3) ^ (n & 7))) << 4) + (kk & 7) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(tile_hi + off) = h;
+    *reinterpret_cast<__nv_bfloat16*>(tile_lo + off) = l;
+}
+
+// one block per layer
+__global__ void __launch_bounds__(256) tf_pack_kernel(TfLayerParams p, uint8_t* __restrict__ blob) {
+    for (int e = threadIdx.x; e < 192 * 64; e += blockDim.x) {
+        const int n = e >> 6, kk = e & 63;
+        const float* src = n < 64 ? p.q : (n < 128 ? p.k : p.v);
+        put_split(blob + kOffQkv, blob + kOffQkv + 24576, n, kk, src[(n & 63) * 64 + kk]);
+    }
+    for (int e = threadIdx.x; e < 64 * 64; e += blockDim.x) {
+        const int n = e >> 6, kk = e & 63;
+        put_split(blob + kOffMerge, blob + kOffMerge + 8192, n, kk, p.merge[e]);
+    }
+    for (int e = threadIdx.x; e < 128 * 128; e += blockDim.x) {
+        const int n = e >> 7, k = e & 127, kc = k >> 6;
+        put_split(blob + kOffMlp0 + kc * 16384, blob + kOffMlp0 + (2 + kc) * 16384, n, k & 63, p.mlp0[e]);
+    }
+    for (int e = threadIdx.x; e < 64 * 128; e += blockDim.x) {
+        const int n = e >> 7, k = e & 127, kc = k >> 6;
+        put_split(blob + kOffMlp2 + kc * 8192, blob + kOffMlp2 + (2 + kc) * 8192, n, k & 63, p.mlp2[e]);
+    }
+    float* ln = reinterpret_cast<float*>(blob + kOffLn);
+    if (threadIdx.x < 64) {
+        ln[threadIdx.x] = p.n1w[threadIdx.x];
+        ln[64 + threadIdx.x] = p.n1b[threadIdx.x];
+        ln[128 + threadIdx.x] = p.n2w[threadIdx.x];
+        ln[192 + threadIdx.x] = p.n2b[threadIdx.x];
+    }
+}
+
+// ---------------------------------------------------------------- device helpers
+// (a, b) -> packed bf16 pair of the high parts and of the residuals a - ah, b - bh
+__device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    hi = *reinterpret_cast<const uint32_t*>(&h);
+    const float ah = __uint_as_float(hi << 16), bh = __uint_as_float(hi & 0xffff0000u);
+    const __nv_bfloat162 l = __floats2bfloat162_rn(a - ah, b - bh);
+    lo = *reinterpret_cast<const uint32_t*>(&l);
+}
+// 32 values of this thread's row -> A operand columns (hi at `thi`, lo at `tlo`, 16 columns each)
+__device__ __forceinline__ void store_operand32(uint32_t thi, uint32_t tlo, const float (&v)[32]) {
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) split2(v[2 * i], v[2 * i + 1], hi[i], lo[i]);
+    tmem_st_32x16(thi, hi);
+    tmem_st_32x16(tlo, lo);
+}
+// elu(x) + 1   (attentions.py:11-12)
+__device__ __forceinline__ float elu1(float x) { return x > 0.f ? x + 1.f : ex2_approx(x * 1.4426950408889634f); }
+
+// mean and centred sum of squares of 32 values
+__device__ __forceinline__ float2 local_stats(const float (&v)[32]) {
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) { s0 += v[i]; s1 += v[i + 1]; }
+    const float mean = (s0 + s1) * (1.f / 32.f);
+    float m0 = 0.f, m1 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) {
+        const float d0 = v[i] - mean, d1 = v[i + 1] - mean;
+        m0 = fmaf(d0, d0, m0);
+        m1 = fmaf(d1, d1, m1);
+    }
+    return make_float2(mean, m0 + m1);
+}
+// LayerNorm over 64 channels from the two halves' statistics (Chan's combination), eps 1e-5
+__device__ __forceinline__ void layer_norm32(float (&v)[32], float2 mine, float2 other, const float* w, const float* b) {
+    const float mean = 0.5f * (mine.x + other.x);
+    const float dm = mine.x - other.x;
+    const float var = (mine.y + other.y + dm * dm * 16.f) * (1.f / 64.f);
+    const float rstd = 1.0f / sqrtf(var + 1e-5f);
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+        const float4 ww = *reinterpret_cast<const float4*>(w + i);
+        const float4 bb = *reinterpret_cast<const float4*>(b + i);
+        v[i] = fmaf((v[i] - mean) * rstd, ww.x, bb.x);
+        v[i + 1] = fmaf((v[i + 1] - mean) * rstd, ww.y, bb.y);
+        v[i + 2] = fmaf((v[i + 2] - mean) * rstd, ww.z, bb.z);
+        v[i + 3] = fmaf((v[i + 3] - mean) * rstd, ww.w, bb.w);
+    }
+}
+
+struct __align__(16) TfCtl {
+    uint64_t w_full;
+    uint64_t to_epi[2];     // MMA warp -> the slot's epilogue warps (tcgen05.commit)
+    uint64_t to_mma[2];     // epilogue warps -> the slot's MMA warp (8 arrivals)
+    uint32_t tmem_base;
+    int lock_owner;         // attention scratch: 0 free, else slot + 1
+    int lock_left;          // warps of the owner still using it
+};
+
+struct TfParams {
+    const float* in[2];
+    float* out[2];
+    const int* count;
+    int capacity;
+    int WW;
+    const uint8_t* blob;
+};
+
+// ---------------------------------------------------------------- one encoder layer
+// kCross = false: 'self'  (both windows updated against themselves, one pass)
+// kCross = true : 'cross' (pass 0: window 0 against window 1; pass 1: window 1 against the
+//                          UPDATED window 0 -- transformer.py:93-95)
+template <bool kCross>
+__global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* blob = smem;
+    uint8_t* scr = smem + kBlobBytes;                                         // K | V rows
+    float* kvm = reinterpret_cast<float*>(scr + kScratchBytes);               // [2 windows][64 d][8 v]
+    float* ksum = kvm + 2 * 64 * 8;                                           // [2][64]
+    float2* lnx = reinterpret_cast<float2*>(ksum + 2 * 64);                   // [2 slots][128 rows][2 halves]
+    TfCtl* ctl = reinterpret_cast<TfCtl*>(lnx + 2 * 128 * 2);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr int kPasses = kCross ? 2 : 1;
+
+    if (threadIdx.x == 0) {
+        mbar_init(&ctl->w_full, 1);
+        for (int s = 0; s < 2; ++s) { mbar_init(&ctl->to_epi[s], 1); mbar_init(&ctl->to_mma[s], 8); }
+        ctl->lock_owner = 0;
+        ctl->lock_left = 0;
+        fence_mbar_init();
+#ifdef FM_DEBUG_WAIT
+        if (blockIdx.x == 0) printf("ctl: w_full@%u to_epi@%u to_mma@%u\n", smem_u32(&ctl->w_full), smem_u32(&ctl->to_epi[0]), smem_u32(&ctl->to_mma[0]));
+#endif
+    }
+    if (warp == 18) tmem_alloc<512>(&ctl->tmem_base);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = ctl->tmem_base;
+    const int M = p.count ? min(*p.count, p.capacity) : p.capacity;
+    const int WW = p.WW;
+
+    if (warp >= 16) {
+        reg_dealloc<40>();
+        if (warp == 18 && lane == 0) {   // -------------------------------- weights -> shared memory
+            mbar_arrive_expect_tx(&ctl->w_full, kBlobBytes);
+            for (int off = 0; off < kBlobBytes; off += 32768)
+                bulk_load_1d(blob + off, p.blob + off, min(32768, kBlobBytes - off), &ctl->w_full);
+        } else if (warp < 18 && lane == 0) {   // -------------------------- MMA issuer of slot `warp - 16`
+            const int slot = warp - 16;
+            const uint32_t ts = tmem_base + slot * kSlotCols;
+            const uint32_t wb = smem_u32(blob);
+            constexpr uint32_t id192 = umma_idesc_bf16_f32(128, 192), id128 = umma_idesc_bf16_f32(128, 128),
+                               id64 = umma_idesc_bf16_f32(128, 64);
+            uint32_t it = 0;
+            auto wait_ops = [&]() { mbar_wait(&ctl->to_mma[slot], it & 1); ++it; tc_fence_after(); };
+            mbar_wait(&ctl->w_full, 0);
+            for (int t = blockIdx.x * 2 + slot; t < M; t += 2 * gridDim.x) {
+                for (int pass = 0; pass < kPasses; ++pass) {
+                    // term 0: a_hi b_hi, term 1: a_hi b_lo, term 2: a_lo b_hi
+                    wait_ops();   // X operand ready: Q|K|V = X Wqkv^T
+#pragma unroll
+                    for (int term = 0; term < 3; ++term)
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma_bf16_ts(ts, ts + (term == 2 ? 224 : 192) + 8 * k,
+                                         umma_desc_k_sw128(wb + kOffQkv + (term == 1 ? 24576 : 0) + 32 * k), id192,
+                                         (term | k) != 0);
+                    umma_commit(&ctl->to_epi[slot]);
+                    wait_ops();   // message ready: merge
+#pragma unroll
+                    for (int term = 0; term < 3; ++term)
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma_bf16_ts(ts, ts + (term == 2 ? 160 : 128) + 8 * k,
+                                         umma_desc_k_sw128(wb + kOffMerge + (term == 1 ? 8192 : 0) + 32 * k), id64,
+                                         (term | k) != 0);
+                    umma_commit(&ctl->to_epi[slot]);
+                    wait_ops();   // LayerNorm-1 output ready: hidden = [x | msg] Wmlp0^T
+#pragma unroll
+                    for (int term = 0; term < 3; ++term)
+#pragma unroll
+                        for (int kk = 0; kk < 8; ++kk) {
+                            const int kc = kk >> 2, k = kk & 3;
+                            const uint32_t a = (kc == 0 ? (term == 2 ? 224 : 192) : (term == 2 ? 160 : 128)) + 8 * k;
+                            umma_bf16_ts(ts, ts + a,
+                                         umma_desc_k_sw128(wb + kOffMlp0 + ((term == 1 ? 2 : 0) + kc) * 16384 + 32 * k),
+                                         id128, (term | kk) != 0);
+                        }
+                    umma_commit(&ctl->to_epi[slot]);
+                    wait_ops();   // relu(hidden) ready: out = hidden Wmlp2^T
+#pragma unroll
+                    for (int term = 0; term < 3; ++term)
+#pragma unroll
+                        for (int kk = 0; kk < 8; ++kk) {
+                            const int kc = kk >> 2, k = kk & 3;
+                            umma_bf16_ts(ts, ts + (term == 2 ? 128 : 192) + 8 * kk,
+                                         umma_desc_k_sw128(wb + kOffMlp2 + ((term == 1 ? 2 : 0) + kc) * 8192 + 32 * k),
+                                         id64, (term | kk) != 0);
+                        }
+                    umma_commit(&ctl->to_epi[slot]);
+                }
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ epilogue warps
+        reg_alloc<104>();   // pool = 640 x 96 (launch) - 128 x 40 (control warps) = 512 x 110
+        const int slot = warp >> 3, g = (warp >> 2) & 1, q = warp & 3;
+        const int st = threadIdx.x & (kSlotThreads - 1);          // thread within the slot
+        const int w = q >> 1, r = (q & 1) * 32 + lane;            // window, window cell
+        const int row = q * 32 + lane;                             // TMEM lane
+        const bool valid = r < WW;
+        const uint32_t tl = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + slot * kSlotCols;
+        const uint32_t bar_id = 1 + slot;
+        const float* ln = reinterpret_cast<const float*>(blob + kOffLn) + 32 * g;
+        float2* lnrow = lnx + (slot * 128 + row) * 2;
+        uint32_t it = 0;
+        auto wait_acc = [&]() { mbar_wait(&ctl->to_epi[slot], it & 1); ++it; tc_fence_after(); };
+        auto signal_mma = [&]() {
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ctl->to_mma[slot]);
+        };
+        mbar_wait(&ctl->w_full, 0);   // LayerNorm parameters live in the blob
+
+        for (int t = blockIdx.x * 2 + slot; t < M; t += 2 * gridDim.x) {
+            float x[32];
+            {
+                const float4* src = reinterpret_cast<const float4*>(p.in[w] + (static_cast<size_t>(t) * WW + (valid ? r : 0)) * kC + 32 * g);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const float4 v = valid ? __ldg(src + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
+                }
+            }
+            store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
+            signal_mma();
+
+#pragma unroll 1
+            for (int pass = 0; pass < kPasses; ++pass) {
+                const bool active = !kCross || w == pass;     // this row is a query row / gets updated
+                const bool is_src = !kCross || w != pass;     // this row supplies keys and values
+                const int srcw = kCross ? (w ^ 1) : w;
+                // ================= attention: Q, K, V -> message =================
+                wait_acc();
+                float qf[32];
+                uint32_t v[32];
+                if (active) {
+                    tmem_ld_32x32(tl + 32 * g, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) qf[i] = elu1(__uint_as_float(v[i]));
+                }
+                if (st == 0) {   // the K | V scratch is shared by the two slots
+                    while (atomicCAS(&ctl->lock_owner, 0, slot + 1) != 0) __nanosleep(64);
+                    ctl->lock_left = 8;
+                }
+                named_bar_sync(bar_id, kSlotThreads);
+                if (is_src) {
+                    uint8_t* rowp = scr + (w * kMaxWW + (valid ? r : 0)) * 512;
+                    const int sw = r & 31;
+                    tmem_ld_32x32(tl + 64 + 32 * g, v);
+                    tmem_ld_wait();
+                    if (valid) {
+#pragma unroll
+                        for (int c = 0; c < 8; ++c)
+                            *reinterpret_cast<float4*>(rowp + (((8 * g + c) ^ sw) << 4)) =
+                                make_float4(elu1(__uint_as_float(v[4 * c])), elu1(__uint_as_float(v[4 * c + 1])),
+                                            elu1(__uint_as_float(v[4 * c + 2])), elu1(__uint_as_float(v[4 * c + 3])));
+                    }
+                    tmem_ld_32x32(tl + 128 + 32 * g, v);
+                    tmem_ld_wait();
+                    if (valid) {
+#pragma unroll
+                        for (int c = 0; c < 8; ++c)
+                            *reinterpret_cast<uint4*>(rowp + (((16 + 8 * g + c) ^ sw) << 4)) =
+                                make_uint4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+                    }
+                }
+                named_bar_sync(bar_id, kSlotThreads);
+                {   // KV[d][v] = sum_r K[r][d] V[r][v] within a head; thread = (window, d, half of the 8 v)
+                    const int w2 = st >> 7, d = (st & 127) >> 1, vh = st & 1;
+                    if (!kCross || w2 != pass) {
+                        const uint8_t* base = scr + w2 * kMaxWW * 512;
+                        const int kc = d >> 2, kw = (d & 3) * 4, vc = 16 + (d >> 3) * 2 + vh;
+                        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, ks = 0.f;
+#pragma unroll 7
+                        for (int rr = 0; rr < WW; ++rr) {
+                            const uint8_t* rp = base + rr * 512;
+                            const int sw = rr & 31;
+                            const float kv = *reinterpret_cast<const float*>(rp + ((kc ^ sw) << 4) + kw);
+                            const float4 vv = *reinterpret_cast<const float4*>(rp + ((vc ^ sw) << 4));
+                            a0 = fmaf(kv, vv.x, a0); a1 = fmaf(kv, vv.y, a1);
+                            a2 = fmaf(kv, vv.z, a2); a3 = fmaf(kv, vv.w, a3);
+                            ks += kv;
+                        }
+                        *reinterpret_cast<float4*>(kvm + (w2 * 64 + d) * 8 + vh * 4) = make_float4(a0, a1, a2, a3);
+                        if (vh == 0) ksum[w2 * 64 + d] = ks;
+                    }
+                }
+                named_bar_sync(bar_id, kSlotThreads);
+                if (active) {
+#pragma unroll
+                    for (int hh = 0; hh < 4; ++hh) {
+                        const int h = 4 * g + hh;
+                        const float* kvp = kvm + (srcw * 64 + h * 8) * 8;
+                        const float* ksp = ksum + srcw * 64 + h * 8;
+                        float den = 1e-6f, m[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) m[j] = 0.f;
+#pragma unroll
+                        for (int dd = 0; dd < 8; ++dd) {
+                            const float qd = qf[hh * 8 + dd];
+                            const float4 ka = *reinterpret_cast<const float4*>(kvp + dd * 8);
+                            const float4 kb = *reinterpret_cast<const float4*>(kvp + dd * 8 + 4);
+                            den = fmaf(qd, ksp[dd], den);
+                            m[0] = fmaf(qd, ka.x, m[0]); m[1] = fmaf(qd, ka.y, m[1]);
+                            m[2] = fmaf(qd, ka.z, m[2]); m[3] = fmaf(qd, ka.w, m[3]);
+                            m[4] = fmaf(qd, kb.x, m[4]); m[5] = fmaf(qd, kb.y, m[5]);
+                            m[6] = fmaf(qd, kb.z, m[6]); m[7] = fmaf(qd, kb.w, m[7]);
+                        }
+                        const float z = 1.0f / den;
+                        uint32_t hi[4], lo[4];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) split2(m[2 * j] * z, m[2 * j + 1] * z, hi[j], lo[j]);
+                        tmem_st_32x4(tl + 128 + 16 * g + 4 * hh, hi);
+                        tmem_st_32x4(tl + 160 + 16 * g + 4 * hh, lo);
+                    }
+                }
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    __threadfence_block();
+                    if (atomicSub(&ctl->lock_left, 1) == 1) atomicExch(&ctl->lock_owner, 0);
+                    mbar_arrive(&ctl->to_mma[slot]);
+                }
+                // ================= merge -> LayerNorm 1 =================
+                wait_acc();
+                float y[32];
+                float2 mine = make_float2(0.f, 0.f);
+                if (active) {
+                    tmem_ld_32x32(tl + 32 * g, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) y[i] = __uint_as_float(v[i]);
+                    mine = local_stats(y);
+                    lnrow[g] = mine;
+                }
+                named_bar_sync(bar_id, kSlotThreads);
+                if (active) {
+                    layer_norm32(y, mine, lnrow[g ^ 1], ln, ln + 64);
+                    store_operand32(tl + 128 + 16 * g, tl + 160 + 16 * g, y);
+                }
+                signal_mma();
+                // ================= MLP hidden: relu =================
+                wait_acc();
+                if (active) {
+#pragma unroll
+                    for (int half = 0; half < 2; ++half) {
+                        tmem_ld_32x32(tl + 64 * g + 32 * half, v);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) y[i] = fmaxf(__uint_as_float(v[i]), 0.f);
+                        store_operand32(tl + 192 + 32 * g + 16 * half, tl + 128 + 32 * g + 16 * half, y);
+                    }
+                }
+                signal_mma();
+                // ================= MLP out -> LayerNorm 2 -> residual =================
+                wait_acc();
+                if (active) {
+                    tmem_ld_32x32(tl + 32 * g, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) y[i] = __uint_as_float(v[i]);
+                    mine = local_stats(y);
+                    lnrow[g] = mine;
+                }
+                named_bar_sync(bar_id, kSlotThreads);
+                if (active) {
+                    layer_norm32(y, mine, lnrow[g ^ 1], ln + 128, ln + 192);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) x[i] += y[i];
+                }
+                if (pass + 1 < kPasses) {
+                    // the hidden activations overwrote this row's X operand: put the new x back
+                    if (active) store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
+                    signal_mma();
+                }
+            }
+            if (valid) {
+                float4* dst = reinterpret_cast<float4*>(p.out[w] + (static_cast<size_t>(t) * WW + r) * kC + 32 * g);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) dst[c] = make_float4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 18) tmem_dealloc<512>(tmem_base);
+}
+
+constexpr size_t kTfSmem = 1024 + kBlobBytes + kScratchBytes + 2 * 64 * 8 * 4 + 2 * 64 * 4 + 2 * 128 * 2 * 8 + sizeof(TfCtl);
+static_assert(kTfSmem <= 232448, "fine transformer shared memory budget");
+
+}  // namespace
+
+bool fine_transformer_supported(int C, int nhead, int WW) { return C == kC && nhead == kHeads && WW >= 1 && WW <= kMaxWW; }
+
+size_t fine_transformer_workspace_bytes(int n_layers) { return static_cast<size_t>(n_layers) * kBlobBytes; }
+
+// layer_ptrs: n_layers x 10 device pointers in the order q, k, v, merge, mlp.0, mlp.2, norm1.weight,
+// norm1.bias, norm2.weight, norm2.bias;  kinds[l]: 0 = 'self', 1 = 'cross'.
+cudaError_t launch_fine_transformer(const float* win0, const float* win1, const int* count, int capacity, int WW,
+                                    int n_layers, const int* kinds, const float* const* layer_ptrs, float* out0,
+                                    float* out1, void* workspace, int num_sms, cudaStream_t st) {
+    uint8_t* blobs = static_cast<uint8_t*>(workspace);
+    for (int l = 0; l < n_layers; ++l) {
+        const float* const* q = layer_ptrs + 10 * l;
+        TfLayerParams lp{q[0], q[1], q[2], q[3], q[4], q[5], q[6], q[7], q[8], q[9]};
+        tf_pack_kernel<<<1, 256, 0, st>>>(lp, blobs + static_cast<size_t>(l) * kBlobBytes);
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(tf_layer_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kTfSmem));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(tf_layer_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kTfSmem));
+    if (e != cudaSuccess) return e;
+    const int grid = std::max(1, std::min(num_sms, (capacity + 1) / 2));
+    for (int l = 0; l < n_layers; ++l) {
+        TfParams p{};
+        // layer 0 reads the caller's windows; later layers update the output in place
+        p.in[0] = l == 0 ? win0 : out0; p.in[1] = l == 0 ? win1 : out1;
+        p.out[0] = out0; p.out[1] = out1;
+        p.count = count; p.capacity = capacity; p.WW = WW;
+        p.blob = blobs + static_cast<size_t>(l) * kBlobBytes;
+        if (kinds[l]) tf_layer_kernel<true><<<grid, kTfThreads, kTfSmem, st>>>(p);
+        else tf_layer_kernel<false><<<grid, kTfThreads, kTfSmem, st>>>(p);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+}  // namespace fm

@@ -173,6 +173,12 @@ cudaError_t launch_fine_match(const void* win0, const void* win1, int dtype, con
                               int capacity, int WW, float scale, float* out0, float* out1, int num_sms,
                               cudaStream_t st);
 
+bool fine_transformer_supported(int C, int nhead, int WW);
+size_t fine_transformer_workspace_bytes(int n_layers);
+cudaError_t launch_fine_transformer(const float* win0, const float* win1, const int* count, int capacity, int WW,
+                                    int n_layers, const int* kinds, const float* const* layer_ptrs, float* out0,
+                                    float* out1, void* workspace, int num_sms, cudaStream_t st);
+
 static bool dtype_ok(int t) { return t == FM_DTYPE_BF16 || t == FM_DTYPE_F32; }
 
 static int check_coarse_args(const void* f0, const void* f1, int dt, int B, int N0, int N1, int C, int h0c, int w0c,
@@ -426,6 +432,42 @@ int fm_fine_match(const void* win0, const void* win1, int win_dtype, const float
     cudaError_t e = launch_fine_match(win0, win1, win_dtype, mkpts0_c, mkpts1_c, mix_w0, mix_b0, mix_w1, mix_b1, count,
                                       capacity, WW, scale, mkpts0_f, mkpts1_f, sms, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return cuda_fail(e, "fine_match launch");
+    return FM_OK;
+}
+
+size_t fm_fine_transformer_workspace_bytes(int n_layers) {
+    return n_layers > 0 ? fine_transformer_workspace_bytes(n_layers) : 0;
+}
+
+int fm_fine_transformer(const float* win0, const float* win1, const int32_t* count, int capacity, int WW, int C,
+                        int nhead, int n_layers, const int32_t* layer_kinds, const float* const* layer_params,
+                        float* out0, float* out1, void* workspace, size_t workspace_bytes, void* stream) {
+    if (!win0 || !win1 || !out0 || !out1 || !layer_kinds || !layer_params || !workspace) { set_error("null pointer argument"); return FM_ERR_BAD_ARG; }
+    if (n_layers < 1 || n_layers > 16 || capacity < 0) { set_error("n_layers must be in [1, 16] and capacity >= 0"); return FM_ERR_BAD_ARG; }
+    if (!fine_transformer_supported(C, nhead, WW)) {
+        set_error("fine transformer supports d_model 64, nhead 8, WW <= 49 (got C=%d nhead=%d WW=%d)", C, nhead, WW);
+        return FM_ERR_UNSUPPORTED;
+    }
+    for (int l = 0; l < n_layers; ++l) {
+        if (layer_kinds[l] != 0 && layer_kinds[l] != 1) { set_error("layer_kinds[%d] must be 0 (self) or 1 (cross)", l); return FM_ERR_BAD_ARG; }
+        for (int k = 0; k < 10; ++k)
+            if (!layer_params[10 * l + k]) { set_error("layer_params[%d] is NULL", 10 * l + k); return FM_ERR_BAD_ARG; }
+    }
+    if ((reinterpret_cast<uintptr_t>(win0) | reinterpret_cast<uintptr_t>(win1) | reinterpret_cast<uintptr_t>(out0) |
+         reinterpret_cast<uintptr_t>(out1) | reinterpret_cast<uintptr_t>(workspace)) & 15) {
+        set_error("window and workspace pointers must be 16-byte aligned");
+        return FM_ERR_BAD_ARG;
+    }
+    if (workspace_bytes < fine_transformer_workspace_bytes(n_layers)) {
+        set_error("fine transformer workspace too small: need %zu bytes, got %zu", fine_transformer_workspace_bytes(n_layers), workspace_bytes);
+        return FM_ERR_WORKSPACE;
+    }
+    if (capacity == 0) return FM_OK;
+    const int sms = sm_count();
+    if (sms <= 0) { set_error("no CUDA device available (this library has no CPU path)"); return FM_ERR_CUDA; }
+    cudaError_t e = launch_fine_transformer(win0, win1, count, capacity, WW, n_layers, layer_kinds, layer_params, out0, out1,
+                                            workspace, sms, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "fine_transformer launch");
     return FM_OK;
 }
 

@@ -339,6 +339,102 @@ class FineMatching(nn.Module):
         data.update({"mkpts1_f": o1})
 
 
+class EncoderLayer(nn.Module):
+    """Parameter holder with the reference's names (network/module/transformer.py:6-32):
+    q_proj / k_proj / v_proj / merge (no bias), mlp.0 / mlp.2 (no bias), norm1 / norm2.  The
+    arithmetic lives in fm_fine_transformer; this module has no forward of its own."""
+
+    def __init__(self, d_model, nhead, attention='linear'):
+        super().__init__()
+        self.dim = d_model // nhead
+        self.nhead = nhead
+        self.q_proj = nn.Linear(d_model, d_model, bias=False)
+        self.k_proj = nn.Linear(d_model, d_model, bias=False)
+        self.v_proj = nn.Linear(d_model, d_model, bias=False)
+        self.merge = nn.Linear(d_model, d_model, bias=False)
+        self.mlp = nn.Sequential(
+            nn.Linear(d_model * 2, d_model * 2, bias=False),
+            nn.ReLU(True),
+            nn.Linear(d_model * 2, d_model, bias=False),
+        )
+        self.norm1 = nn.LayerNorm(d_model)
+        self.norm2 = nn.LayerNorm(d_model)
+
+    def flat_parameters(self):
+        return [self.q_proj.weight, self.k_proj.weight, self.v_proj.weight, self.merge.weight,
+                self.mlp[0].weight, self.mlp[2].weight, self.norm1.weight, self.norm1.bias,
+                self.norm2.weight, self.norm2.bias]
+
+    def forward(self, *a, **k):
+        raise NotImplementedError("EncoderLayer (B200) only holds parameters; call the "
+                                  "enclosing LocalFeatureTransformer")
+
+
+class LocalFeatureTransformer(nn.Module):
+    """network/module/transformer.py:59-97 for the FINE windows ([M, WW, 64], 8 heads, linear
+    attention) on the tcgen05 encoder-layer kernel.  Same constructor dict, parameter names
+    (`layers.{i}.q_proj.weight` ...) and forward signature as the reference."""
+
+    def __init__(self, config):
+        super().__init__()
+        self.config = config
+        self.d_model = config['d_model']
+        self.nhead = config['nhead']
+        self.layer_names = list(config['layer_names'])
+        if config.get('attention', 'linear') != 'linear':
+            raise _lib.FmError("LocalFeatureTransformer (B200) implements attention='linear' only")
+        for name in self.layer_names:
+            if name not in ('self', 'cross'):
+                raise KeyError(name)
+        self.layers = nn.ModuleList([EncoderLayer(self.d_model, self.nhead)
+                                     for _ in self.layer_names])
+        self._ws = _Workspace()
+        self._reset_parameters()
+
+    def _reset_parameters(self):   # transformer.py:73-76
+        for p in self.parameters():
+            if p.dim() > 1:
+                nn.init.xavier_uniform_(p)
+
+    def transform(self, feat0, feat1, count=None, out=None):
+        """Device-side call: [cap, WW, C] fp32 windows -> updated windows (`out` may be the
+        inputs themselves); `count` = device int32 match count for padded buffers."""
+        import ctypes
+        lib = _lib.load()
+        _require_cuda(feat0, feat1)
+        f0 = feat0.to(torch.float32).contiguous()
+        f1 = feat1.to(torch.float32).contiguous()
+        cap, WW, C = f0.shape
+        dev = f0.device
+        o0, o1 = out if out is not None else (torch.empty_like(f0), torch.empty_like(f1))
+        if cap == 0:
+            return o0, o1
+        n = len(self.layers)
+        params = [t.detach().to(device=dev, dtype=torch.float32).contiguous()
+                  for layer in self.layers for t in layer.flat_parameters()]
+        kinds = (ctypes.c_int32 * n)(*[0 if k == 'self' else 1 for k in self.layer_names])
+        ptrs = (ctypes.c_void_p * (10 * n))(*[t.data_ptr() for t in params])
+        nbytes = lib.fm_fine_transformer_workspace_bytes(n)
+        ws = self._ws.get(nbytes, dev)
+        with torch.cuda.device(dev):
+            rc = lib.fm_fine_transformer(_lib.ptr(f0), _lib.ptr(f1), _lib.ptr(count), cap, WW, C,
+                                         self.nhead, n, kinds, ptrs, _lib.ptr(o0), _lib.ptr(o1),
+                                         _lib.ptr(ws), nbytes, _lib.stream_ptr(dev))
+        _lib.check(rc, "fm_fine_transformer")
+        self._keepalive = params   # the launch is asynchronous
+        return o0, o1
+
+    def forward(self, feat0, feat1, mask0=None, mask1=None):
+        """Same contract as transformer.py:78-97 (masks must be None, as at net.py:80)."""
+        assert self.d_model == feat0.size(2), "the feature number of src and transformer must be equal"
+        if mask0 is not None or mask1 is not None:
+            raise NotImplementedError("LocalFeatureTransformer (B200): masks are not supported")
+        if self.training:
+            raise NotImplementedError("LocalFeatureTransformer (B200) is inference-only")
+        with torch.no_grad():
+            return self.transform(feat0, feat1)
+
+
 def install(net):
     """Swaps the three hot-path modules of a constructed reference `net` (network/net.py:29-32)
     for the B200 ones, carrying the trained parameters over.  Returns `net`."""
@@ -357,5 +453,12 @@ def install(net):
     net.coarse_matching = cm.to(dev)
     net.fine_preprocess = fp.to(dev)
     net.fine_matching = fm.to(dev)
+    fine_cfg = cfg['fine']
+    if (hasattr(net, 'fine') and fine_cfg.get('attention', 'linear') == 'linear'
+            and fine_cfg['d_model'] == 64 and fine_cfg['nhead'] == 8 and cfg['fine_window_size'] ** 2 <= 49):
+        ft = LocalFeatureTransformer(fine_cfg)
+        ft.load_state_dict(net.fine.state_dict(), strict=True)
+        net._fm_reference['fine'] = net.fine
+        net.fine = ft.to(dev)
     net.train(False)
     return net

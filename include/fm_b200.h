@@ -9,6 +9,8 @@
  *                         network/module/fine_preprocess.py:32-62       (called at network/net.py:78)
  *   fm_fine_match    <->  FineMatching.forward
  *                         network/utils/fine_matching_new.py:22-79      (called at network/net.py:83)
+ *   fm_fine_transformer <-> LocalFeatureTransformer.forward on the fine windows
+ *                         network/module/transformer.py:78-97           (called at network/net.py:80)
  *
  * Conventions
  *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless stated;
@@ -145,6 +147,27 @@ FM_API int fm_fine_match(const void* win0, const void* win1, int win_dtype, cons
                   const float* mkpts1_c, const float* mix_w0, const float* mix_b0,
                   const float* mix_w1, const float* mix_b1, const int32_t* count, int capacity,
                   int WW, int Cf, float scale, float* mkpts0_f, float* mkpts1_f, void* stream);
+
+/* ---------------------------------------------------------------- fine stage: window transformer
+ * LocalFeatureTransformer on the gathered windows -- the step between fm_fine_gather and
+ * fm_fine_match (network/net.py:79-80 -> network/module/transformer.py:78-97; EncoderLayer
+ * transformer.py:34-57 with LinearAttention attentions.py:22-46, no masks):
+ *   'self' : feat0 = layer(feat0, feat0); feat1 = layer(feat1, feat1)
+ *   'cross': feat0 = layer(feat0, feat1); feat1 = layer(feat1, feat0)      (the UPDATED feat0)
+ * win0/win1, out0/out1: float [capacity, WW, C]; out may alias win (in place).  C must be 64,
+ * nhead 8, WW <= 49 (the shipped fine config, demo/net_config.py:40-44).
+ * layer_kinds: HOST array [n_layers], 0 = 'self', 1 = 'cross'.
+ * layer_params: HOST array [n_layers * 10] of DEVICE pointers to the fp32 parameters of each
+ *   layer in state-dict order q_proj.weight [C,C], k_proj.weight, v_proj.weight, merge.weight,
+ *   mlp.0.weight [2C,2C], mlp.2.weight [C,2C], norm1.weight [C], norm1.bias, norm2.weight, norm2.bias.
+ * workspace: fm_fine_transformer_workspace_bytes(n_layers) bytes, 16-byte aligned (packed weights).
+ * All GEMMs run on the tensor cores with fp32-grade 3-term bf16 splits; entries >= *count are
+ * not touched. */
+FM_API size_t fm_fine_transformer_workspace_bytes(int n_layers);
+FM_API int fm_fine_transformer(const float* win0, const float* win1, const int32_t* count, int capacity,
+                        int WW, int C, int nhead, int n_layers, const int32_t* layer_kinds,
+                        const float* const* layer_params, float* out0, float* out1, void* workspace,
+                        size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------- match records
  * Packs the match list into 40-byte records for the cross-GPU gather (the analogue of the

@@ -135,6 +135,32 @@ def fine_match_special(ref, name, seed):
     print(f"{name}: std range {data['mkpts0_f'][:, 2].min():.3e} .. {data['mkpts0_f'][:, 2].max():.4f}")
 
 
+def transformer_case(ref, name, M, layer_names, seed):
+    """The reference's fine LocalFeatureTransformer (network/module/transformer.py:59-97) on
+    bf16-representable windows, LayerNorm affine parameters randomised so they matter."""
+    cfg = dict(reference_shims.default_config()["fine"], layer_names=list(layer_names))
+    torch.manual_seed(seed)
+    t = ref.LocalFeatureTransformer(cfg).eval()
+    with torch.no_grad():
+        for layer in t.layers:
+            for ln in (layer.norm1, layer.norm2):
+                ln.weight.uniform_(0.5, 1.5)
+                ln.bias.uniform_(-0.3, 0.3)
+    g = torch.Generator().manual_seed(seed + 1)
+    win0 = torch.randn(M, 49, 64, generator=g).mul(1.5).to(torch.bfloat16).float()
+    win1 = (win0 + 0.5 * torch.randn(M, 49, 64, generator=g)).to(torch.bfloat16).float()
+    win0[0] = 0.0                       # an all-zero window: LayerNorm of a constant row
+    win1[1] *= 32.0                     # large magnitudes (power of two: stays bf16-exact)
+    with torch.no_grad():
+        o0, o1 = t(win0, win1)
+    sd = {"sd." + k: v.numpy() for k, v in t.state_dict().items()}
+    np.savez_compressed(
+        os.path.join(GOLDEN_DIR, name + ".npz"),
+        win0=bf16_bits(win0), win1=bf16_bits(win1), out0=o0.numpy(), out1=o1.numpy(),
+        layer_names=np.array(list(layer_names)), nhead=cfg["nhead"], **sd)
+    print(f"{name}: M={M} layers={list(layer_names)} |out| max {o0.abs().max():.3f}")
+
+
 def main():
     os.makedirs(GOLDEN_DIR, exist_ok=True)
     ref = reference_shims.load_reference()
@@ -148,6 +174,8 @@ def main():
     coarse_case(ref, "coarse_hot", 1, (8, 10), (8, 10), "planted", 0.5, 16, sigma=3.0)
     fine_case(ref, "fine_chain", (8, 10), 40, 21)
     fine_match_special(ref, "fine_match_special", 31)
+    transformer_case(ref, "fine_transformer", 12, ("self", "cross"), 41)
+    transformer_case(ref, "fine_transformer_csc", 5, ("cross", "self", "cross"), 42)
 
 
 if __name__ == "__main__":

@@ -210,3 +210,67 @@ def match_head(feat_c0, feat_c1, feat_f0, feat_f1, hw0_i, hw0_c, hw1_c, hw0_f,
     out["mkpts0_f"], out["mkpts1_f"] = fine_match(win0, win1, out["mkpts0_c"], out["mkpts1_c"],
                                                   fine_params, hw0_i, hw0_f, dtype)
     return out
+
+
+# --------------------------------------------------------------------------- fine transformer
+def _linear_attention(q, k, v, nhead, eps=1e-6):
+    """Multi-head linear attention on [M, L, C] projections.
+
+    network/module/attentions.py:11-12   feature map elu(x) + 1
+    network/module/attentions.py:40-44   values / S; KV = K^T V per head; Z = 1 / (Q . sum_s K + eps);
+                                         out = (Q KV) Z * S
+    """
+    M, L, C = q.shape
+    S = k.shape[1]
+    d = C // nhead
+    Q = torch.nn.functional.elu(q).add(1).view(M, L, nhead, d)
+    K = torch.nn.functional.elu(k).add(1).view(M, S, nhead, d)
+    V = v.view(M, S, nhead, d) / S
+    KV = torch.einsum("nshd,nshv->nhdv", K, V)
+    Z = 1 / (torch.einsum("nlhd,nhd->nlh", Q, K.sum(dim=1)) + eps)
+    out = torch.einsum("nlhd,nhdv,nlh->nlhv", Q, KV, Z) * S
+    return out.reshape(M, L, C)
+
+
+def encoder_layer(x, source, p, nhead, dtype=torch.float32):
+    """EncoderLayer.forward with attention == 'linear' and no masks.
+
+    network/module/transformer.py:46-51  q/k/v projections (no bias), attention, merge, LayerNorm 1
+    network/module/transformer.py:54-57  mlp(cat[x, message]) = W2 relu(W1 .), LayerNorm 2, residual
+    `p` = dict(q, k, v, merge [C, C]; mlp0 [2C, 2C]; mlp2 [C, 2C]; norm1_w, norm1_b, norm2_w, norm2_b [C]).
+    """
+    F = torch.nn.functional
+    C = x.shape[-1]
+    g = lambda name: p[name].to(dtype)
+    msg = _linear_attention(F.linear(x, g("q")), F.linear(source, g("k")), F.linear(source, g("v")), nhead)
+    msg = F.layer_norm(F.linear(msg, g("merge")), (C,), g("norm1_w"), g("norm1_b"), 1e-5)
+    msg = F.linear(torch.relu(F.linear(torch.cat([x, msg], -1), g("mlp0"))), g("mlp2"))
+    msg = F.layer_norm(msg, (C,), g("norm2_w"), g("norm2_b"), 1e-5)
+    return x + msg
+
+
+def local_feature_transformer(feat0, feat1, layers, layer_names, nhead, dtype=torch.float32):
+    """LocalFeatureTransformer.forward (network/module/transformer.py:78-97): 'self' updates both
+    sides against themselves; 'cross' updates feat0 against feat1, then feat1 against the UPDATED
+    feat0.  `layers` = list of per-layer parameter dicts (see encoder_layer)."""
+    f0, f1 = feat0.to(dtype), feat1.to(dtype)
+    for p, name in zip(layers, layer_names):
+        if name == "self":
+            f0 = encoder_layer(f0, f0, p, nhead, dtype)
+            f1 = encoder_layer(f1, f1, p, nhead, dtype)
+        elif name == "cross":
+            f0 = encoder_layer(f0, f1, p, nhead, dtype)
+            f1 = encoder_layer(f1, f0, p, nhead, dtype)
+    return f0, f1
+
+
+def transformer_params_from_state_dict(sd, n_layers, prefix=""):
+    """Per-layer dicts from LocalFeatureTransformer state-dict keys (`layers.{i}.q_proj.weight` ...)."""
+    out = []
+    for i in range(n_layers):
+        k = f"{prefix}layers.{i}."
+        out.append({"q": sd[k + "q_proj.weight"], "k": sd[k + "k_proj.weight"], "v": sd[k + "v_proj.weight"],
+                    "merge": sd[k + "merge.weight"], "mlp0": sd[k + "mlp.0.weight"], "mlp2": sd[k + "mlp.2.weight"],
+                    "norm1_w": sd[k + "norm1.weight"], "norm1_b": sd[k + "norm1.bias"],
+                    "norm2_w": sd[k + "norm2.weight"], "norm2_b": sd[k + "norm2.bias"]})
+    return out

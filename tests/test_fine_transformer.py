@@ -1,0 +1,134 @@
+"""Fine LocalFeatureTransformer (network/module/transformer.py:59-97):
+oracle vs the reference's golden outputs (CPU) and the tcgen05 kernel vs both (GPU, through the
+C ABI).  Tolerance: 2e-4 absolute on O(1..10) features -- the 3-term bf16 split GEMMs are
+fp32-grade (2^-17 relative per product); downstream fine coordinates stay within 1e-3 px."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import compare, matcher_oracle as mo, reference_shims
+
+CASES = ["fine_transformer", "fine_transformer_csc"]
+
+
+def load(golden_dir, name):
+    g = dict(np.load(os.path.join(golden_dir, name + ".npz")))
+    sd = {k[3:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("sd.")}
+    names = [str(x) for x in g["layer_names"]]
+    return g, sd, names
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_transformer_oracle_matches_reference_golden(golden_dir, name):
+    torch.set_num_threads(1)
+    g, sd, names = load(golden_dir, name)
+    layers = mo.transformer_params_from_state_dict(sd, len(names))
+    o0, o1 = mo.local_feature_transformer(compare.from_bits(g["win0"]), compare.from_bits(g["win1"]),
+                                          layers, names, int(g["nhead"]))
+    np.testing.assert_allclose(o0.numpy(), g["out0"], rtol=0, atol=2e-5)
+    np.testing.assert_allclose(o1.numpy(), g["out1"], rtol=0, atol=2e-5)
+
+
+@pytest.mark.skipif(not reference_shims.available(), reason="reference tree not present")
+def test_transformer_oracle_matches_live_reference():
+    ref = reference_shims.load_reference()
+    cfg = dict(reference_shims.default_config()["fine"], layer_names=["self", "cross", "self"])
+    torch.manual_seed(5)
+    t = ref.LocalFeatureTransformer(cfg).eval()
+    x0, x1 = torch.randn(9, 49, 64), torch.randn(9, 49, 64)
+    with torch.no_grad():
+        r0, r1 = t(x0, x1)
+    layers = mo.transformer_params_from_state_dict(t.state_dict(), 3)
+    o0, o1 = mo.local_feature_transformer(x0, x1, layers, cfg["layer_names"], 8)
+    assert torch.allclose(o0, r0, atol=1e-5) and torch.allclose(o1, r1, atol=1e-5)
+
+
+# ------------------------------------------------------------------------------------ GPU
+def _module(sd, names):
+    from featurematching_b200 import modules
+    m = modules.LocalFeatureTransformer({"d_model": 64, "nhead": 8, "layer_names": names,
+                                         "attention": "linear"}).eval()
+    m.load_state_dict(sd, strict=True)
+    return m.cuda()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", CASES)
+def test_transformer_kernel_matches_reference_golden(golden_dir, name):
+    g, sd, names = load(golden_dir, name)
+    m = _module(sd, names)
+    w0, w1 = compare.from_bits(g["win0"]).cuda(), compare.from_bits(g["win1"]).cuda()
+    o0, o1 = m(w0, w1)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(o0.cpu().numpy(), g["out0"], rtol=0, atol=2e-4)
+    np.testing.assert_allclose(o1.cpu().numpy(), g["out1"], rtol=0, atol=2e-4)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,names", [(1, ["self"]), (2, ["cross"]), (3, ["self", "cross"]),
+                                     (700, ["self", "cross"]), (4001, ["cross", "self"])])
+def test_transformer_kernel_vs_oracle(M, names):
+    from featurematching_b200 import modules
+    torch.manual_seed(100 + M)
+    m = modules.LocalFeatureTransformer({"d_model": 64, "nhead": 8, "layer_names": names,
+                                         "attention": "linear"}).eval()
+    with torch.no_grad():
+        for layer in m.layers:
+            layer.norm1.weight.uniform_(0.5, 1.5); layer.norm1.bias.uniform_(-0.3, 0.3)
+            layer.norm2.weight.uniform_(0.5, 1.5); layer.norm2.bias.uniform_(-0.3, 0.3)
+    x0 = torch.randn(M, 49, 64)
+    x1 = x0 + 0.4 * torch.randn(M, 49, 64)
+    layers = mo.transformer_params_from_state_dict(m.state_dict(), len(names))
+    r0, r1 = mo.local_feature_transformer(x0, x1, layers, names, 8)
+    mc = m.cuda()
+    # padded buffers + device-side count: rows >= count must stay untouched
+    cap = M + 5
+    p0 = torch.full((cap, 49, 64), 7.0, device="cuda"); p0[:M] = x0.cuda()
+    p1 = torch.full((cap, 49, 64), 7.0, device="cuda"); p1[:M] = x1.cuda()
+    count = torch.tensor([M], dtype=torch.int32, device="cuda")
+    o0, o1 = mc.transform(p0, p1, count=count, out=(p0, p1))   # in place
+    torch.cuda.synchronize()
+    assert (o0[M:] == 7.0).all() and (o1[M:] == 7.0).all()
+    e0 = (o0[:M].cpu() - r0).abs().max().item()
+    e1 = (o1[:M].cpu() - r1).abs().max().item()
+    assert e0 < 2e-4 and e1 < 2e-4, (e0, e1)
+
+
+@pytest.mark.gpu
+def test_transformer_then_fine_match_within_1e3_px():
+    """gather-free check of the north_star tolerance through transformer + fine matching."""
+    from featurematching_b200 import modules, synth
+    torch.manual_seed(9)
+    M = 1500
+    names = ["self", "cross"]
+    m = modules.LocalFeatureTransformer({"d_model": 64, "nhead": 8, "layer_names": names,
+                                         "attention": "linear"}).eval()
+    x0 = torch.randn(M, 49, 64)
+    x1 = x0 + 0.3 * torch.randn(M, 49, 64)
+    p = synth.hot_path_params(seed=3)
+    mk = torch.rand(M, 2).mul(400).floor()
+    layers = mo.transformer_params_from_state_dict(m.state_dict(), 2)
+    r0, r1 = mo.local_feature_transformer(x0, x1, layers, names, 8)
+    ref0, ref1 = mo.fine_match(r0, r1, mk, mk, p, (512, 640), (256, 320))
+    fm = modules.FineMatching({}).cuda()
+    with torch.no_grad():
+        fm.mix_feat_0.weight.copy_(p["mix_w0"][None]); fm.mix_feat_0.bias.copy_(p["mix_b0"].reshape(1))
+        fm.mix_feat_1.weight.copy_(p["mix_w1"][None]); fm.mix_feat_1.bias.copy_(p["mix_b1"].reshape(1))
+    o0, o1 = m.cuda()(x0.cuda(), x1.cuda())
+    k0, k1 = fm.refine(o0, o1, mk.cuda(), mk.cuda(), 2.0)
+    torch.cuda.synchronize()
+    assert (k0[:, :2].cpu() - ref0[:, :2]).abs().max() < 1e-3
+    assert (k1[:, :2].cpu() - ref1[:, :2]).abs().max() < 1e-3
+
+
+@pytest.mark.gpu
+def test_transformer_rejects_unsupported():
+    from featurematching_b200 import _lib, modules
+    m = modules.LocalFeatureTransformer({"d_model": 64, "nhead": 8, "layer_names": ["self"],
+                                         "attention": "linear"}).cuda().eval()
+    with pytest.raises(_lib.FmError):
+        m(torch.zeros(2, 64, 64, device="cuda"), torch.zeros(2, 64, 64, device="cuda"))   # WW = 64 > 49
+    with pytest.raises(_lib.FmError):
+        m(torch.zeros(2, 49, 64), torch.zeros(2, 49, 64))   # CPU tensors: no fallback
