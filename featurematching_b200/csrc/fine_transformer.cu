@@ -46,7 +46,10 @@ constexpr int kOffMlp0 = 65536;        // [2][2 K chunks][128 x 128 B]
 constexpr int kOffMlp2 = 131072;       // [2][2 K chunks][64 x 128 B]
 constexpr int kOffLn = 163840;         // norm1.weight, norm1.bias, norm2.weight, norm2.bias: 4 x 64 fp32
 constexpr int kBlobBytes = 164864;
-constexpr int kScratchBytes = 2 * kMaxWW * 512;   // K | V fp32 of both windows, one 512-byte row per cell
+constexpr int kScrRow = 528;          // K | V fp32 of one cell (512 B) + 16 B pad: rows r and r + 8 share banks, so
+                                      // a warp's 32 row-strided 16-byte stores take the minimum 4 wavefronts and
+                                      // the reduction reads rows at compile-time offsets
+constexpr int kScratchBytes = 2 * kMaxWW * kScrRow;
 
 struct TfLayerParams {
     const float* q; const float* k; const float* v; const float* merge;
@@ -142,6 +145,18 @@ __device__ __forceinline__ void layer_norm32(float (&v)[32], float2 mine, float2
     }
 }
 
+#ifdef FM_TF_ONE_SLOT   // debug: slot 1 idle
+#define TF_T0 (slot ? M : blockIdx.x)
+#define TF_DT gridDim.x
+#else
+#define TF_T0 (blockIdx.x * 2 + slot)
+#define TF_DT (2 * gridDim.x)
+#endif
+
+#ifdef FM_TF_TRACE
+__device__ long long g_trace[32];
+#endif
+
 struct __align__(16) TfCtl {
     uint64_t w_full;
     uint64_t to_epi[2];     // MMA warp -> the slot's epilogue warps (tcgen05.commit)
@@ -164,10 +179,12 @@ struct TfParams {
 // kCross = false: 'self'  (both windows updated against themselves, one pass)
 // kCross = true : 'cross' (pass 0: window 0 against window 1; pass 1: window 1 against the
 //                          UPDATED window 0 -- transformer.py:93-95)
-template <bool kCross>
+// kWW = window cells when known at compile time (49: the shipped 7 x 7 window), 0 = read p.WW
+template <bool kCross, int kWW>
 __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams p) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    // aligned by OFFSET (not through an integer cast) so the compiler keeps the shared address space
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* blob = smem;
     uint8_t* scr = smem + kBlobBytes;                                         // K | V rows
     float* kvm = reinterpret_cast<float*>(scr + kScratchBytes);               // [2 windows][64 d][8 v]
@@ -193,10 +210,10 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
     tc_fence_after();
     const uint32_t tmem_base = ctl->tmem_base;
     const int M = p.count ? min(*p.count, p.capacity) : p.capacity;
-    const int WW = p.WW;
+    const int WW = kWW ? kWW : p.WW;
 
     if (warp >= 16) {
-        reg_dealloc<40>();
+        reg_dealloc<56>();
         if (warp == 18 && lane == 0) {   // -------------------------------- weights -> shared memory
             mbar_arrive_expect_tx(&ctl->w_full, kBlobBytes);
             for (int off = 0; off < kBlobBytes; off += 32768)
@@ -207,55 +224,75 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
             const uint32_t wb = smem_u32(blob);
             constexpr uint32_t id192 = umma_idesc_bf16_f32(128, 192), id128 = umma_idesc_bf16_f32(128, 128),
                                id64 = umma_idesc_bf16_f32(128, 64);
+            const uint64_t d_qkv = umma_desc_k_sw128(wb + kOffQkv), d_merge = umma_desc_k_sw128(wb + kOffMerge),
+                           d_mlp0 = umma_desc_k_sw128(wb + kOffMlp0), d_mlp2 = umma_desc_k_sw128(wb + kOffMlp2);
             uint32_t it = 0;
+#ifdef FM_TF_PHASE_CLOCK
+            long long mw[4] = {0, 0, 0, 0}, mi[4] = {0, 0, 0, 0}, mt = clock64();
+            auto wait_ops = [&]() { const int ph = it & 3; mi[(ph + 3) & 3] += clock64() - mt; mt = clock64();
+                                    mbar_wait(&ctl->to_mma[slot], it & 1); ++it; tc_fence_after();
+                                    mw[ph] += clock64() - mt; mt = clock64(); };
+#elif defined(FM_TF_TRACE)
+            auto wait_ops = [&]() { if (blockIdx.x == 0 && slot == 0 && (it >> 2) == 3 && (it & 3)) g_trace[15 + 2 * (it & 3)] = clock64();
+                                    if (blockIdx.x == 0 && slot == 0 && it == 16) g_trace[23] = clock64();
+                                    mbar_wait(&ctl->to_mma[slot], it & 1); tc_fence_after();
+                                    if (blockIdx.x == 0 && slot == 0 && (it >> 2) == 3) g_trace[16 + 2 * (it & 3)] = clock64();
+                                    ++it; };
+#else
             auto wait_ops = [&]() { mbar_wait(&ctl->to_mma[slot], it & 1); ++it; tc_fence_after(); };
+#endif
             mbar_wait(&ctl->w_full, 0);
-            for (int t = blockIdx.x * 2 + slot; t < M; t += 2 * gridDim.x) {
+            for (int t = TF_T0; t < M; t += TF_DT) {
                 for (int pass = 0; pass < kPasses; ++pass) {
-                    // term 0: a_hi b_hi, term 1: a_hi b_lo, term 2: a_lo b_hi
+                    // term 0: a_hi b_hi, term 1: a_hi b_lo, term 2: a_lo b_hi.  The loops over terms are
+                    // NOT unrolled and descriptors are base + offset: fully unrolled, the 72 descriptors
+                    // become loop invariants that spill (the issuing thread then waits on local memory
+                    // for every MMA: 280 cycles per instruction instead of 50).
                     wait_ops();   // X operand ready: Q|K|V = X Wqkv^T
+#pragma unroll 1
+                    for (int term = 0; term < 3; ++term) {
+                        const uint32_t a = ts + (term == 2 ? 224 : 192);
+                        const uint64_t b = d_qkv + (term == 1 ? 24576 / 16 : 0);
 #pragma unroll
-                    for (int term = 0; term < 3; ++term)
-#pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            umma_bf16_ts(ts, ts + (term == 2 ? 224 : 192) + 8 * k,
-                                         umma_desc_k_sw128(wb + kOffQkv + (term == 1 ? 24576 : 0) + 32 * k), id192,
-                                         (term | k) != 0);
+                        for (int k = 0; k < 4; ++k) umma_bf16_ts(ts, a + 8 * k, b + 2 * k, id192, (term | k) != 0);
+                    }
                     umma_commit(&ctl->to_epi[slot]);
                     wait_ops();   // message ready: merge
+#pragma unroll 1
+                    for (int term = 0; term < 3; ++term) {
+                        const uint32_t a = ts + (term == 2 ? 160 : 128);
+                        const uint64_t b = d_merge + (term == 1 ? 8192 / 16 : 0);
 #pragma unroll
-                    for (int term = 0; term < 3; ++term)
-#pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            umma_bf16_ts(ts, ts + (term == 2 ? 160 : 128) + 8 * k,
-                                         umma_desc_k_sw128(wb + kOffMerge + (term == 1 ? 8192 : 0) + 32 * k), id64,
-                                         (term | k) != 0);
+                        for (int k = 0; k < 4; ++k) umma_bf16_ts(ts, a + 8 * k, b + 2 * k, id64, (term | k) != 0);
+                    }
                     umma_commit(&ctl->to_epi[slot]);
                     wait_ops();   // LayerNorm-1 output ready: hidden = [x | msg] Wmlp0^T
-#pragma unroll
+#pragma unroll 1
                     for (int term = 0; term < 3; ++term)
+#pragma unroll 1
+                        for (int kc = 0; kc < 2; ++kc) {
+                            const uint32_t a = ts + (kc == 0 ? (term == 2 ? 224 : 192) : (term == 2 ? 160 : 128));
+                            const uint64_t b = d_mlp0 + ((term == 1 ? 2 : 0) + kc) * (16384 / 16);
 #pragma unroll
-                        for (int kk = 0; kk < 8; ++kk) {
-                            const int kc = kk >> 2, k = kk & 3;
-                            const uint32_t a = (kc == 0 ? (term == 2 ? 224 : 192) : (term == 2 ? 160 : 128)) + 8 * k;
-                            umma_bf16_ts(ts, ts + a,
-                                         umma_desc_k_sw128(wb + kOffMlp0 + ((term == 1 ? 2 : 0) + kc) * 16384 + 32 * k),
-                                         id128, (term | kk) != 0);
+                            for (int k = 0; k < 4; ++k) umma_bf16_ts(ts, a + 8 * k, b + 2 * k, id128, (term | kc | k) != 0);
                         }
                     umma_commit(&ctl->to_epi[slot]);
                     wait_ops();   // relu(hidden) ready: out = hidden Wmlp2^T
-#pragma unroll
+#pragma unroll 1
                     for (int term = 0; term < 3; ++term)
+#pragma unroll 1
+                        for (int kc = 0; kc < 2; ++kc) {
+                            const uint32_t a = ts + (term == 2 ? 128 : 192) + 32 * kc;
+                            const uint64_t b = d_mlp2 + ((term == 1 ? 2 : 0) + kc) * (8192 / 16);
 #pragma unroll
-                        for (int kk = 0; kk < 8; ++kk) {
-                            const int kc = kk >> 2, k = kk & 3;
-                            umma_bf16_ts(ts, ts + (term == 2 ? 128 : 192) + 8 * kk,
-                                         umma_desc_k_sw128(wb + kOffMlp2 + ((term == 1 ? 2 : 0) + kc) * 8192 + 32 * k),
-                                         id64, (term | kk) != 0);
+                            for (int k = 0; k < 4; ++k) umma_bf16_ts(ts, a + 8 * k, b + 2 * k, id64, (term | kc | k) != 0);
                         }
                     umma_commit(&ctl->to_epi[slot]);
                 }
             }
+#ifdef FM_TF_PHASE_CLOCK
+            if (blockIdx.x == 0) printf("mma warp %d: wait %lld %lld %lld %lld  issue %lld %lld %lld %lld\n", warp, mw[0], mw[1], mw[2], mw[3], mi[0], mi[1], mi[2], mi[3]);
+#endif
         }
     } else {
         // ------------------------------------------------------------------ epilogue warps
@@ -278,8 +315,17 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
             if (lane == 0) mbar_arrive(&ctl->to_mma[slot]);
         };
         mbar_wait(&ctl->w_full, 0);   // LayerNorm parameters live in the blob
+#ifdef FM_TF_PHASE_CLOCK
+        long long pc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, pt = clock64();
+#define TF_TICK(k) { const long long now_ = clock64(); pc[k] += now_ - pt; pt = now_; }
+#elif defined(FM_TF_TRACE)
+        int tile_no = 0;
+#define TF_TICK(k) { if (blockIdx.x == 0 && warp == 0 && lane == 0 && tile_no == 3) g_trace[k] = clock64(); }
+#else
+#define TF_TICK(k)
+#endif
 
-        for (int t = blockIdx.x * 2 + slot; t < M; t += 2 * gridDim.x) {
+        for (int t = TF_T0; t < M; t += TF_DT) {
             float x[32];
             {
                 const float4* src = reinterpret_cast<const float4*>(p.in[w] + (static_cast<size_t>(t) * WW + (valid ? r : 0)) * kC + 32 * g);
@@ -291,6 +337,9 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
             }
             store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
             signal_mma();
+            if (valid && t + TF_DT < M)   // this thread's 128 bytes of the slot's next tile -> L2
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(p.in[w] + (static_cast<size_t>(t + TF_DT) * WW + r) * kC + 32 * g));
+            TF_TICK(0)
 
 #pragma unroll 1
             for (int pass = 0; pass < kPasses; ++pass) {
@@ -299,6 +348,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                 const int srcw = kCross ? (w ^ 1) : w;
                 // ================= attention: Q, K, V -> message =================
                 wait_acc();
+                TF_TICK(1)
                 float qf[32];
                 uint32_t v[32];
                 if (active) {
@@ -312,15 +362,15 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     ctl->lock_left = 8;
                 }
                 named_bar_sync(bar_id, kSlotThreads);
+                TF_TICK(2)
                 if (is_src) {
-                    uint8_t* rowp = scr + (w * kMaxWW + (valid ? r : 0)) * 512;
-                    const int sw = r & 31;
+                    uint8_t* rowp = scr + (w * kMaxWW + (valid ? r : 0)) * kScrRow;
                     tmem_ld_32x32(tl + 64 + 32 * g, v);
                     tmem_ld_wait();
                     if (valid) {
 #pragma unroll
                         for (int c = 0; c < 8; ++c)
-                            *reinterpret_cast<float4*>(rowp + (((8 * g + c) ^ sw) << 4)) =
+                            *reinterpret_cast<float4*>(rowp + ((8 * g + c) << 4)) =
                                 make_float4(elu1(__uint_as_float(v[4 * c])), elu1(__uint_as_float(v[4 * c + 1])),
                                             elu1(__uint_as_float(v[4 * c + 2])), elu1(__uint_as_float(v[4 * c + 3])));
                     }
@@ -329,32 +379,34 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     if (valid) {
 #pragma unroll
                         for (int c = 0; c < 8; ++c)
-                            *reinterpret_cast<uint4*>(rowp + (((16 + 8 * g + c) ^ sw) << 4)) =
+                            *reinterpret_cast<uint4*>(rowp + ((16 + 8 * g + c) << 4)) =
                                 make_uint4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
                     }
                 }
                 named_bar_sync(bar_id, kSlotThreads);
+                TF_TICK(3)
                 {   // KV[d][v] = sum_r K[r][d] V[r][v] within a head; thread = (window, d, half of the 8 v)
                     const int w2 = st >> 7, d = (st & 127) >> 1, vh = st & 1;
                     if (!kCross || w2 != pass) {
-                        const uint8_t* base = scr + w2 * kMaxWW * 512;
-                        const int kc = d >> 2, kw = (d & 3) * 4, vc = 16 + (d >> 3) * 2 + vh;
+                        const uint8_t* kp = scr + w2 * kMaxWW * kScrRow + d * 4;
+                        const uint8_t* vp = scr + w2 * kMaxWW * kScrRow + 256 + (d >> 3) * 32 + vh * 16;
                         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, ks = 0.f;
-#pragma unroll 7
-                        for (int rr = 0; rr < WW; ++rr) {
-                            const uint8_t* rp = base + rr * 512;
-                            const int sw = rr & 31;
-                            const float kv = *reinterpret_cast<const float*>(rp + ((kc ^ sw) << 4) + kw);
-                            const float4 vv = *reinterpret_cast<const float4*>(rp + ((vc ^ sw) << 4));
-                            a0 = fmaf(kv, vv.x, a0); a1 = fmaf(kv, vv.y, a1);
-                            a2 = fmaf(kv, vv.z, a2); a3 = fmaf(kv, vv.w, a3);
-                            ks += kv;
+#pragma unroll
+                        for (int rr = 0; rr < kMaxWW; ++rr) {
+                            if (kWW ? rr < kWW : rr < WW) {
+                                const float kv = *reinterpret_cast<const float*>(kp + rr * kScrRow);
+                                const float4 vv = *reinterpret_cast<const float4*>(vp + rr * kScrRow);
+                                a0 = fmaf(kv, vv.x, a0); a1 = fmaf(kv, vv.y, a1);
+                                a2 = fmaf(kv, vv.z, a2); a3 = fmaf(kv, vv.w, a3);
+                                ks += kv;
+                            }
                         }
                         *reinterpret_cast<float4*>(kvm + (w2 * 64 + d) * 8 + vh * 4) = make_float4(a0, a1, a2, a3);
                         if (vh == 0) ksum[w2 * 64 + d] = ks;
                     }
                 }
                 named_bar_sync(bar_id, kSlotThreads);
+                TF_TICK(4)
                 if (active) {
 #pragma unroll
                     for (int hh = 0; hh < 4; ++hh) {
@@ -391,8 +443,10 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     if (atomicSub(&ctl->lock_left, 1) == 1) atomicExch(&ctl->lock_owner, 0);
                     mbar_arrive(&ctl->to_mma[slot]);
                 }
+                TF_TICK(5)
                 // ================= merge -> LayerNorm 1 =================
                 wait_acc();
+                TF_TICK(6)
                 float y[32];
                 float2 mine = make_float2(0.f, 0.f);
                 if (active) {
@@ -409,8 +463,10 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     store_operand32(tl + 128 + 16 * g, tl + 160 + 16 * g, y);
                 }
                 signal_mma();
+                TF_TICK(7)
                 // ================= MLP hidden: relu =================
                 wait_acc();
+                TF_TICK(8)
                 if (active) {
 #pragma unroll
                     for (int half = 0; half < 2; ++half) {
@@ -422,8 +478,10 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     }
                 }
                 signal_mma();
+                TF_TICK(9)
                 // ================= MLP out -> LayerNorm 2 -> residual =================
                 wait_acc();
+                TF_TICK(10)
                 if (active) {
                     tmem_ld_32x32(tl + 32 * g, v);
                     tmem_ld_wait();
@@ -449,11 +507,30 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
 #pragma unroll
                 for (int c = 0; c < 8; ++c) dst[c] = make_float4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
             }
+            TF_TICK(11)
+#ifdef FM_TF_TRACE
+            ++tile_no;
+#endif
         }
+#ifdef FM_TF_PHASE_CLOCK
+        if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 13))
+            printf("warp %d cycles: load %lld | waitQKV %lld lock %lld kvstore %lld kvsum %lld msg %lld | waitMerge %lld ln1 %lld | waitHid %lld relu %lld | waitOut %lld ln2+store %lld\n",
+                   warp, pc[0], pc[1], pc[2], pc[3], pc[4], pc[5], pc[6], pc[7], pc[8], pc[9], pc[10], pc[11]);
+#endif
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+#ifdef FM_TF_TRACE
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        const long long t0 = g_trace[0];
+        printf("epi : opsX %lld | accQKV %lld lock %lld kvst %lld kvsum %lld msgdone %lld | accMerge %lld ln1done %lld | accHid %lld reludone %lld | accOut %lld end %lld\n",
+               0ll, g_trace[1] - t0, g_trace[2] - t0, g_trace[3] - t0, g_trace[4] - t0, g_trace[5] - t0, g_trace[6] - t0, g_trace[7] - t0,
+               g_trace[8] - t0, g_trace[9] - t0, g_trace[10] - t0, g_trace[11] - t0);
+        printf("mma : seenX %lld issuedQKV %lld | seenMsg %lld issuedMerge %lld | seenLn1 %lld issuedMlp1 %lld | seenRelu %lld issuedMlp2 %lld\n",
+               g_trace[16] - t0, g_trace[17] - t0, g_trace[18] - t0, g_trace[19] - t0, g_trace[20] - t0, g_trace[21] - t0, g_trace[22] - t0, g_trace[23] - t0);
+    }
+#endif
     if (warp == 18) tmem_dealloc<512>(tmem_base);
 }
 
@@ -479,10 +556,13 @@ cudaError_t launch_fine_transformer(const float* win0, const float* win1, const 
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(tf_layer_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kTfSmem));
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(tf_layer_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kTfSmem));
-    if (e != cudaSuccess) return e;
+    using Kern = void (*)(const TfParams);
+    const Kern kern[2] = {WW == 49 ? tf_layer_kernel<false, 49> : tf_layer_kernel<false, 0>,
+                          WW == 49 ? tf_layer_kernel<true, 49> : tf_layer_kernel<true, 0>};
+    for (int k = 0; k < 2; ++k) {
+        e = cudaFuncSetAttribute(kern[k], cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kTfSmem));
+        if (e != cudaSuccess) return e;
+    }
     const int grid = std::max(1, std::min(num_sms, (capacity + 1) / 2));
     for (int l = 0; l < n_layers; ++l) {
         TfParams p{};
@@ -491,8 +571,7 @@ cudaError_t launch_fine_transformer(const float* win0, const float* win1, const 
         p.out[0] = out0; p.out[1] = out1;
         p.count = count; p.capacity = capacity; p.WW = WW;
         p.blob = blobs + static_cast<size_t>(l) * kBlobBytes;
-        if (kinds[l]) tf_layer_kernel<true><<<grid, kTfThreads, kTfSmem, st>>>(p);
-        else tf_layer_kernel<false><<<grid, kTfThreads, kTfSmem, st>>>(p);
+        kern[kinds[l] ? 1 : 0]<<<grid, kTfThreads, kTfSmem, st>>>(p);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
