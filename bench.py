@@ -6,7 +6,8 @@
 One step = one pass of the hot path (coarse dual-softmax mutual-NN match -> fine window gather ->
 fine dual-correlate match -> match-record pack [+ cross-GPU gather when N > 1]) over one batch of
 synthetic frame pairs: BASELINE.json configs[1], 32 planted 640x512-shaped pairs per GPU, bf16
-features.  The out-of-scope fine transformer is not part of the step.
+features.  The fine transformer is timed beside the step and reported
+under kernels.fine_transformer; --with-fine-transformer puts it inside the step on both arms.
 Prints ONE JSON line (rank 0).  `--impl reference` times the CPU restatement of the reference
 (oracle/, the reference itself cannot travel to the GPU box) on the host cores instead.
 """
@@ -56,6 +57,10 @@ def parse_args():
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--with-fine-transformer", action="store_true",
+                    help="put the fine LocalFeatureTransformer (SURVEY.md 8(f) rank 1, net.py:79-80) INSIDE the step, "
+                         "between gather and fine match (GPU and CPU arms alike); by default it is timed beside "
+                         "the step and reported under kernels.fine_transformer with in_step = false")
     a = ap.parse_args()
     preset = CONFIGS[a.config]
     for k in ("pairs", "height", "width"):
@@ -136,6 +141,18 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------ CPU arm
+FINE_CFG = {"d_model": 64, "nhead": 8, "layer_names": ["self", "cross"], "attention": "linear"}   # demo/net_config.py:40-44
+
+
+def fine_transformer_module():
+    """The B200 LocalFeatureTransformer with seeded random weights (no checkpoint exists offline);
+    the CPU arms read the same weights through its state dict."""
+    import torch
+    from featurematching_b200 import modules
+    torch.manual_seed(77)
+    return modules.LocalFeatureTransformer(FINE_CFG).eval()
+
+
 def cpu_head_factory(args):
     """The oracle's match head on one synthetic pair (same generator as the GPU arm)."""
     import torch
@@ -152,9 +169,14 @@ def cpu_head_factory(args):
         ff0, ff1 = synth.fine_features(1, 64, hw_f[0], hw_f[1], 4321 + k, channels_last=False)
         return fc0, fc1, ff0, ff1
 
+    ft = None
+    if args.with_fine_transformer:
+        layers = mo.transformer_params_from_state_dict(fine_transformer_module().state_dict(), len(FINE_CFG["layer_names"]))
+        ft = lambda w0, w1: mo.local_feature_transformer(w0, w1, layers, FINE_CFG["layer_names"], FINE_CFG["nhead"])
+
     def run_pair(inp):
         with torch.no_grad():
-            out = mo.match_head(*inp, hw_i, hw_c, hw_c, hw_f, cfg["match_coarse"], p, p)
+            out = mo.match_head(*inp, hw_i, hw_c, hw_c, hw_f, cfg["match_coarse"], p, p, fine_transformer=ft)
         return int(out["b_ids"].numel())
 
     return make_pair, run_pair, cores
@@ -231,7 +253,7 @@ def run_b200(args):
     hw_i, hw_c, hw_f, N = shapes(args)
     B = args.pairs
     cfg = {"fine_window_size": 7, "fine_concat_coarse_feat": True, "coarse": {"d_model": 256},
-           "fine": {"d_model": 64},
+           "fine": FINE_CFG,
            "match_coarse": {"thr": 0.2, "border_rm": 2, "dsmax_temperature": 0.1}}
 
     # synthetic inputs, resident in HBM (seeds differ per rank and pair)
@@ -245,7 +267,8 @@ def run_b200(args):
         fc0, fc1, _ = synth.coarse_features(B, N, N, 256, args.noise, "planted", 1234 + rank * B, device=dev,
                                              sigma=args.sigma)
         ff0, ff1 = synth.fine_features(B, 64, hw_f[0], hw_f[1], 4321 + rank, device=dev)
-    head = pipeline.MatchHead(cfg, dev)
+    ftm = fine_transformer_module().to(dev)
+    head = pipeline.MatchHead(cfg, dev, fine_transformer=ftm if args.with_fine_transformer else None)
     head.load_params(synth.hot_path_params(seed=99))
     in_bytes = sum(t.numel() * t.element_size() for t in (fc0, fc1, ff0, ff1))
 
@@ -267,7 +290,7 @@ def run_b200(args):
     # ---- timed region: K steps, device timers, stage events inside
     K = args.steps
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(1)]
-    stage_ev = [[torch.cuda.Event(enable_timing=True) for _ in range(5)] for _ in range(K)]
+    stage_ev = [[torch.cuda.Event(enable_timing=True) for _ in range(6)] for _ in range(K)]
     sampler = ClockSampler(local) if rank == 0 else None
     lib.fm_profile_enable(1)
     if sampler:
@@ -285,6 +308,9 @@ def run_b200(args):
         pre.gather(ff0, ff1, fc0, fc1, c.b_ids, c.i_ids, c.j_ids, hw_c, hw_c, hw_f, count=c.status,
                    capacity=r.capacity, out=(r.win0, r.win1))
         e[2].record()
+        if args.with_fine_transformer:
+            ftm.transform(r.win0, r.win1, count=c.status, out=(r.win0, r.win1))
+        e[5].record()
         fin.refine(r.win0, r.win1, c.mkpts0_c, c.mkpts1_c, float(hw_i[0]) / hw_f[0], count=c.status,
                    out=(r.mkpts0_f, r.mkpts1_f))
         e[3].record()
@@ -308,7 +334,23 @@ def run_b200(args):
         ms_total = float(t.item())
     M_end = head.check_status(r)
     assert M_end == M, "match count changed between steps"
-    stage_ms = [sum(stage_ev[k][s].elapsed_time(stage_ev[k][s + 1]) for k in range(K)) / K for s in range(4)]
+    def span(a, b):
+        return sum(stage_ev[k][a].elapsed_time(stage_ev[k][b]) for k in range(K)) / K
+    stage_ms = [span(0, 1), span(1, 2), span(5, 3), span(3, 4)]
+    ft_ms = span(2, 5)
+    if not args.with_fine_transformer:
+        # timed beside the step, on the step's own windows (separate output buffers)
+        o = (torch.empty_like(r.win0), torch.empty_like(r.win1))
+        for _ in range(2):
+            ftm.transform(r.win0, r.win1, count=r.coarse.status, out=o)
+        fe = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        fe[0].record()
+        for _ in range(5):
+            ftm.transform(r.win0, r.win1, count=r.coarse.status, out=o)
+        fe[1].record()
+        torch.cuda.synchronize()
+        ft_ms = fe[0].elapsed_time(fe[1]) / 5
+        del o
     ms_step = ms_total / K
     value = world * B * K / (ms_total * 1e-3)
 
@@ -355,10 +397,18 @@ def run_b200(args):
         "fine_match": {"bound": "hbm", "ms": stage_ms[2], "achieved": match_bytes / (stage_ms[2] * 1e-3) / 1e9,
                        "peak": pk["hbm_gbs"], "unit": "GB/s"},
     }
+    # fine transformer: 4 encoder-layer applications per match (self x 2 sides, cross x 2), each
+    # 49 rows x (q,k,v,merge 4 x 64x64 + mlp 128x128 + 64x128) MACs = 4.01 MFLOP; fp32-grade GEMMs
+    # run as 3 bf16 tensor-core terms, so the ALGORITHMIC flop below is a third of what the pipe executes
+    ft_flops = M * 4 * 49 * 2.0 * (4 * 64 * 64 + 128 * 128 + 64 * 128)
+    kernels["fine_transformer"] = {"bound": "tensor", "ms": ft_ms, "achieved": ft_flops / (ft_ms * 1e-3) / 1e12,
+                                   "peak": pk["tflops_sustained"], "unit": "TFLOP/s",
+                                   "in_step": bool(args.with_fine_transformer),
+                                   "note": "fp32-equivalent flop; executed as 3-term bf16 splits, SIMT/latency-bound"}
     for kname, kv in kernels.items():
         kv["frac"] = kv["achieved"] / kv["peak"]
         kv["share_of_step"] = kv["ms"] / ms_step
-    top = max(kernels, key=lambda n: kernels[n]["ms"])
+    top = max((n for n in kernels if kernels[n].get("in_step", True)), key=lambda n: kernels[n]["ms"])
     traffic = load_traffic(top)
     roofline = dict(kernels[top], kernel=top, traffic=traffic, peak_source=pk["source"] +
                     (" (sustained bf16)" if kernels[top]["bound"] == "tensor" else " (copy)"))
@@ -369,16 +419,17 @@ def run_b200(args):
         "dtype": "bf16", "data": "synthetic",
         "config": {"workload": f"{B} planted {args.width}x{args.height} pairs/GPU/step ({CONFIGS[args.config]['name']}"
                                + (", consecutive frames of one sequence" if args.sequence else "") + "): "
-                               "coarse match + fine gather + fine match + record pack"
+                               "coarse match + fine gather + " + ("fine transformer + " if args.with_fine_transformer else "")
+                               + "fine match + record pack"
                                + (" + NCCL all_gather of match records" if world > 1 else ""),
                    "N0": N, "N1": N, "C": 256, "fine_map": [64, hw_f[0], hw_f[1]], "window": 7,
                    "matches_per_step": M, "thr": 0.2, "border_rm": 2, "temperature": 0.1,
                    "l2": f"inputs ({in_bytes / 1e6:.0f} MB/step) exceed the 126 MB L2; no explicit flush",
                    "windows": "fp32 (what the reference hands to its fine transformer)"},
         "roofline": roofline, "kernels": kernels,
-        "stage_ms": {"coarse_total": stage_ms[0], "fine_gather": stage_ms[1], "fine_match": stage_ms[2],
-                     "pack_and_gather": stage_ms[3]},
-        "e2e": e2e, "gpu_launches": K * LAUNCHES_PER_STEP, "clocks": clocks,
+        "stage_ms": {"coarse_total": stage_ms[0], "fine_gather": stage_ms[1], "fine_transformer": ft_ms,
+                     "fine_match": stage_ms[2], "pack_and_gather": stage_ms[3]},
+        "e2e": e2e, "gpu_launches": K * (LAUNCHES_PER_STEP + (4 if args.with_fine_transformer else 0)), "clocks": clocks,
     }
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args)

@@ -1,8 +1,7 @@
 """Sync-free matching head for a batch of frame pairs, and the cross-GPU match-list gather.
 
 `MatchHead` chains the three drop-in modules of modules.py the way network/net.py:75-83 does
-(coarse match -> window gather -> [fine transformer, out of scope, optional callable] -> fine
-match), but keeps the match count on the device: every buffer is sized for `capacity` matches
+(coarse match -> window gather -> [fine LocalFeatureTransformer, optional] -> fine match), but keeps the match count on the device: every buffer is sized for `capacity` matches
 and the kernels read the count from the coarse status word, so a batch costs one host
 synchronisation (at the caller's choosing) instead of the reference's one per stage
 (torch.where at coarse_matching_new.py:109, the shape test at fine_preprocess.py:37).
@@ -38,6 +37,14 @@ class MatchHead:
         self.fine_preprocess = modules.FinePreprocess(config).eval().to(self.device)
         self.fine_preprocess.out_dtype = window_dtype
         self.fine_matching = modules.FineMatching(config['fine']).eval().to(self.device)
+        # fine LocalFeatureTransformer (network/net.py:79-80): True builds the B200 module from
+        # config['fine'] (random init, load a state dict into head.fine_transformer), a
+        # modules.LocalFeatureTransformer is used as given (both stay sync-free), any other
+        # callable is treated as a foreign PyTorch module (needs exact-length inputs: one sync)
+        if fine_transformer is True:
+            fine_transformer = modules.LocalFeatureTransformer(config['fine'])
+        if isinstance(fine_transformer, modules.LocalFeatureTransformer):
+            fine_transformer = fine_transformer.eval().to(self.device)
         self.fine_transformer = fine_transformer
         self._res = None
         self._host = {}
@@ -95,8 +102,12 @@ class MatchHead:
             pre.gather(feat_f0, feat_f1, feat_c0, feat_c1, c.b_ids, c.i_ids, c.j_ids, hw0_c, hw1_c,
                        hw0_f, count=count, capacity=r.capacity, out=(r.win0, r.win1))
             w0, w1 = r.win0, r.win1
-            if self.fine_transformer is not None:
-                # out-of-scope PyTorch module (network/net.py:79-80); needs exact-length inputs
+            if isinstance(self.fine_transformer, modules.LocalFeatureTransformer):
+                if r.win0.dtype != torch.float32:
+                    raise _lib.FmError("the fine transformer kernel takes fp32 windows")
+                self.fine_transformer.transform(r.win0, r.win1, count=count, out=(r.win0, r.win1))
+            elif self.fine_transformer is not None:
+                # foreign PyTorch module; needs exact-length inputs
                 M = int(count[0].item())
                 w0, w1 = self.fine_transformer(r.win0[:M], r.win1[:M])
             scale = float(hw0_i[0]) / float(hw0_f[0])

@@ -132,3 +132,34 @@ def test_transformer_rejects_unsupported():
         m(torch.zeros(2, 64, 64, device="cuda"), torch.zeros(2, 64, 64, device="cuda"))   # WW = 64 > 49
     with pytest.raises(_lib.FmError):
         m(torch.zeros(2, 49, 64), torch.zeros(2, 49, 64))   # CPU tensors: no fallback
+
+
+@pytest.mark.gpu
+def test_match_head_with_fine_transformer_vs_oracle():
+    """coarse -> gather -> fine transformer -> fine match, sync-free MatchHead against the oracle
+    chain (net.py:75-83 with the transformer in place): ids exact, coordinates within 1e-3 px."""
+    from featurematching_b200 import modules, pipeline, synth
+    hw_c, hw_f, hw_i = (40, 40), (160, 160), (320, 320)
+    N, B = 1600, 2
+    fc0, fc1, _ = synth.coarse_features(B, N, N, 256, 0.1, "planted", 3)
+    ff0, ff1 = synth.fine_features(B, 64, 160, 160, 8)
+    p = synth.hot_path_params(seed=4)
+    fine_cfg = {"d_model": 64, "nhead": 8, "layer_names": ["self", "cross"], "attention": "linear"}
+    cfg = {"fine_window_size": 7, "fine_concat_coarse_feat": True, "coarse": {"d_model": 256}, "fine": fine_cfg,
+           "match_coarse": {"thr": 0.2, "border_rm": 2, "dsmax_temperature": 0.1}}
+    torch.manual_seed(21)
+    ft = modules.LocalFeatureTransformer(fine_cfg).eval()
+    layers = mo.transformer_params_from_state_dict(ft.state_dict(), 2)
+    ref = mo.match_head(fc0, fc1, ff0, ff1, hw_i, hw_c, hw_c, hw_f, cfg["match_coarse"], p, p,
+                        fine_transformer=lambda a, b: mo.local_feature_transformer(a, b, layers, fine_cfg["layer_names"], 8))
+    head = pipeline.MatchHead(cfg, "cuda", fine_transformer=ft)
+    head.load_params(p)
+    dev = torch.device("cuda")
+    r = head.run(fc0.to(dev), fc1.to(dev), ff0.to(dev), ff1.to(dev), hw_i, hw_c, hw_c, hw_f)
+    M = head.check_status(r)
+    assert M == ref["b_ids"].numel() and M > 2000
+    assert torch.equal(r.coarse.i_ids[:M].cpu(), ref["i_ids"]) and torch.equal(r.coarse.j_ids[:M].cpu(), ref["j_ids"])
+    compare.check_fine(r.mkpts0_f[:M], r.mkpts1_f[:M], ref["mkpts0_f"], ref["mkpts1_f"])
+    # without the transformer the coordinates differ: the stage is really in the chain
+    ref_plain = mo.match_head(fc0, fc1, ff0, ff1, hw_i, hw_c, hw_c, hw_f, cfg["match_coarse"], p, p)
+    assert (ref_plain["mkpts0_f"][:, :2] - ref["mkpts0_f"][:, :2]).abs().max() > 1e-2
