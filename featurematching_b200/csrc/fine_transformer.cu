@@ -145,6 +145,9 @@ __device__ __forceinline__ void layer_norm32(float (&v)[32], float2 mine, float2
     }
 }
 
+#ifndef TF_SLEEP
+#define TF_SLEEP 64
+#endif
 #ifdef FM_TF_ONE_SLOT   // debug: slot 1 idle
 #define TF_T0 (slot ? M : blockIdx.x)
 #define TF_DT gridDim.x
@@ -239,7 +242,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                                     if (blockIdx.x == 0 && slot == 0 && (it >> 2) == 3) g_trace[16 + 2 * (it & 3)] = clock64();
                                     ++it; };
 #else
-            auto wait_ops = [&]() { mbar_wait_sleepy(&ctl->to_mma[slot], it & 1); ++it; tc_fence_after(); };
+            auto wait_ops = [&]() { mbar_wait_backoff<20>(&ctl->to_mma[slot], it & 1); ++it; tc_fence_after(); };
 #endif
             mbar_wait(&ctl->w_full, 0);
             for (int t = TF_T0; t < M; t += TF_DT) {
@@ -307,7 +310,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
         const float* ln = reinterpret_cast<const float*>(blob + kOffLn) + 32 * g;
         float2* lnrow = lnx + (slot * 128 + row) * 2;
         uint32_t it = 0;
-        auto wait_acc = [&]() { mbar_wait_sleepy(&ctl->to_epi[slot], it & 1); ++it; tc_fence_after(); };
+        auto wait_acc = [&]() { mbar_wait_backoff<TF_SLEEP>(&ctl->to_epi[slot], it & 1); ++it; tc_fence_after(); };
         auto signal_mma = [&]() {
             tmem_st_wait();
             tc_fence_before();

@@ -85,12 +85,15 @@ __device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parit
         : "memory");
     return ok != 0;
 }
-// Bounded wait built on the hinted form (traps after ~2 s like mbar_wait).
-__device__ __forceinline__ void mbar_wait_sleepy(uint64_t* bar, uint32_t parity) {
+// Bounded wait that backs off with nanosleep between polls: a waiting warp leaves the issue slots
+// to the warps that have work (a tight try_wait loop competes with them on the same scheduler).
+template <int kSleepNs>
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     uint32_t spins = 0;
-    while (!mbar_try_wait_hint(bar, parity, 20000u)) {
-        if (++spins > 100000u) __trap();
+    while (!mbar_try_wait(bar, parity)) {
+        __nanosleep(kSleepNs);
+        if (++spins > 20000000u) __trap();
     }
 }
 
