@@ -97,6 +97,23 @@ def test_transformer_kernel_vs_oracle(M, names):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("WW", [1, 9, 25, 48])
+def test_transformer_kernel_small_windows(WW):
+    """window sizes below 7 x 7 take the runtime-WW instantiation of the kernel"""
+    from featurematching_b200 import modules
+    torch.manual_seed(WW)
+    names = ["self", "cross"]
+    m = modules.LocalFeatureTransformer({"d_model": 64, "nhead": 8, "layer_names": names,
+                                         "attention": "linear"}).eval()
+    x0, x1 = torch.randn(37, WW, 64), torch.randn(37, WW, 64)
+    layers = mo.transformer_params_from_state_dict(m.state_dict(), 2)
+    r0, r1 = mo.local_feature_transformer(x0, x1, layers, names, 8)
+    o0, o1 = m.cuda()(x0.cuda(), x1.cuda())
+    torch.cuda.synchronize()
+    assert (o0.cpu() - r0).abs().max() < 2e-4 and (o1.cpu() - r1).abs().max() < 2e-4
+
+
+@pytest.mark.gpu
 def test_transformer_then_fine_match_within_1e3_px():
     """gather-free check of the north_star tolerance through transformer + fine matching."""
     from featurematching_b200 import modules, synth
