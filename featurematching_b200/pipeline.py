@@ -247,6 +247,52 @@ def gather_matches(records, capacity, group=None):
     return out
 
 
+class OverlappedGather:
+    """The match-list all_gather on a side stream, so that step k's exchange overlaps step k + 1's
+    kernels ("gather once per batch, overlap with the next batch's compute").
+
+        g = OverlappedGather(device)
+        for batch in batches:
+            r = head.run(..., pack=False)          # everything but the record pack
+            g.before_pack()                        # the records buffer is free again
+            pack records into r.records
+            out = g.launch(r.records, r.capacity)  # valid after g.finish() / the next before_pack()
+        g.finish()
+
+    The records buffer is read by the collective while the next step computes; `before_pack`
+    makes the next pack wait for it (an event wait on the device, no host synchronisation)."""
+
+    def __init__(self, device, group=None):
+        self.device = torch.device(device)
+        self.group = group
+        self.side = torch.cuda.Stream(device=self.device)
+        self.packed = torch.cuda.Event()
+        self.done = torch.cuda.Event()
+        self.pending = False
+        self.out = None
+
+    def before_pack(self):
+        if self.pending:
+            torch.cuda.current_stream(self.device).wait_event(self.done)
+
+    def launch(self, records, capacity):
+        cur = torch.cuda.current_stream(self.device)
+        self.packed.record(cur)
+        self.side.wait_event(self.packed)
+        with torch.cuda.stream(self.side):
+            self.out = gather_matches(records, capacity, self.group)
+            self.done.record(self.side)
+        self.pending = True
+        return self.out
+
+    def finish(self):
+        """Joins the side stream into the current one (device-side); returns the last result."""
+        if self.pending:
+            torch.cuda.current_stream(self.device).wait_event(self.done)
+            self.pending = False
+        return self.out
+
+
 def shard_pairs(num_pairs, rank, world):
     """Contiguous block partition of frame pairs over ranks: [begin, end)."""
     base, rem = divmod(num_pairs, world)
