@@ -145,21 +145,6 @@ __device__ __forceinline__ void layer_norm32(float (&v)[32], float2 mine, float2
     }
 }
 
-#ifndef TF_SLEEP
-#define TF_SLEEP 64
-#endif
-#ifdef FM_TF_ONE_SLOT   // debug: slot 1 idle
-#define TF_T0 (slot ? M : blockIdx.x)
-#define TF_DT gridDim.x
-#else
-#define TF_T0 (blockIdx.x * 2 + slot)
-#define TF_DT (2 * gridDim.x)
-#endif
-
-#ifdef FM_TF_TRACE
-__device__ long long g_trace[32];
-#endif
-
 struct __align__(16) TfCtl {
     uint64_t w_full;
     uint64_t to_epi[2];     // MMA warp -> the slot's epilogue warps (tcgen05.commit)
@@ -179,9 +164,16 @@ struct TfParams {
 };
 
 // ---------------------------------------------------------------- one encoder layer
-// kCross = false: 'self'  (both windows updated against themselves, one pass)
-// kCross = true : 'cross' (pass 0: window 0 against window 1; pass 1: window 1 against the
-//                          UPDATED window 0 -- transformer.py:93-95)
+// kCross = false, 'self': a work item is ONE match; TMEM lanes 0.. = its image-0 window, lanes 64.. =
+//   its image-1 window; one pass updates both (each window attends to itself).
+// kCross = true, 'cross': a work item is a PAIR of matches (a, b) and a tile holds the SAME side of
+//   both: lanes 0.. = match a, lanes 64.. = match b.  Pass 0 (transformer.py:94): the image-1 windows
+//   go through the K|V projection only (their keys/values -> the per-window KV matrices), then the
+//   image-0 windows take the tile, get their Q and run the rest of the layer against those matrices.
+//   Pass 1 (transformer.py:95): the UPDATED image-0 windows are still in the tile's operand columns and
+//   supply K|V; the image-1 windows are read again (L2) and updated.  Every lane of a pass is a row
+//   that is being updated -- no half of the tile idles (the first version kept one match per tile and
+//   spent two half-empty passes on it: 12.4 ms per 125 k matches).
 // kWW = window cells when known at compile time (49: the shipped 7 x 7 window), 0 = read p.WW
 template <bool kCross, int kWW>
 __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams p) {
@@ -189,10 +181,10 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
     // aligned by OFFSET (not through an integer cast) so the compiler keeps the shared address space
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* blob = smem;
-    uint8_t* scr = smem + kBlobBytes;                                         // K | V rows
-    float* kvm = reinterpret_cast<float*>(scr + kScratchBytes);               // [2 windows][64 d][8 v]
-    float* ksum = kvm + 2 * 64 * 8;                                           // [2][64]
-    float2* lnx = reinterpret_cast<float2*>(ksum + 2 * 64);                   // [2 slots][128 rows][2 halves]
+    uint8_t* scr = smem + kBlobBytes;                                         // K | V rows (both slots, locked)
+    float* kvm_all = reinterpret_cast<float*>(scr + kScratchBytes);           // [2 slots][2 windows][64 d][8 v]
+    float* ksum_all = kvm_all + 2 * 2 * 64 * 8;                               // [2 slots][2][64]
+    float2* lnx = reinterpret_cast<float2*>(ksum_all + 2 * 2 * 64);           // [2 slots][128 rows][2 halves]
     TfCtl* ctl = reinterpret_cast<TfCtl*>(lnx + 2 * 128 * 2);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     constexpr int kPasses = kCross ? 2 : 1;
@@ -203,9 +195,6 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
         ctl->lock_owner = 0;
         ctl->lock_left = 0;
         fence_mbar_init();
-#ifdef FM_DEBUG_WAIT
-        if (blockIdx.x == 0) printf("ctl: w_full@%u to_epi@%u to_mma@%u\n", smem_u32(&ctl->w_full), smem_u32(&ctl->to_epi[0]), smem_u32(&ctl->to_mma[0]));
-#endif
     }
     if (warp == 18) tmem_alloc<512>(&ctl->tmem_base);
     tc_fence_before();
@@ -214,6 +203,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
     const uint32_t tmem_base = ctl->tmem_base;
     const int M = p.count ? min(*p.count, p.capacity) : p.capacity;
     const int WW = kWW ? kWW : p.WW;
+    const int items = kCross ? (M + 1) / 2 : M;
 
     if (warp >= 16) {
         reg_dealloc<56>();
@@ -230,36 +220,31 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
             const uint64_t d_qkv = umma_desc_k_sw128(wb + kOffQkv), d_merge = umma_desc_k_sw128(wb + kOffMerge),
                            d_mlp0 = umma_desc_k_sw128(wb + kOffMlp0), d_mlp2 = umma_desc_k_sw128(wb + kOffMlp2);
             uint32_t it = 0;
-#ifdef FM_TF_PHASE_CLOCK
-            long long mw[4] = {0, 0, 0, 0}, mi[4] = {0, 0, 0, 0}, mt = clock64();
-            auto wait_ops = [&]() { const int ph = it & 3; mi[(ph + 3) & 3] += clock64() - mt; mt = clock64();
-                                    mbar_wait(&ctl->to_mma[slot], it & 1); ++it; tc_fence_after();
-                                    mw[ph] += clock64() - mt; mt = clock64(); };
-#elif defined(FM_TF_TRACE)
-            auto wait_ops = [&]() { if (blockIdx.x == 0 && slot == 0 && (it >> 2) == 3 && (it & 3)) g_trace[15 + 2 * (it & 3)] = clock64();
-                                    if (blockIdx.x == 0 && slot == 0 && it == 16) g_trace[23] = clock64();
-                                    mbar_wait(&ctl->to_mma[slot], it & 1); tc_fence_after();
-                                    if (blockIdx.x == 0 && slot == 0 && (it >> 2) == 3) g_trace[16 + 2 * (it & 3)] = clock64();
-                                    ++it; };
-#else
             auto wait_ops = [&]() { mbar_wait_backoff<20>(&ctl->to_mma[slot], it & 1); ++it; tc_fence_after(); };
-#endif
-            mbar_wait(&ctl->w_full, 0);
-            for (int t = TF_T0; t < M; t += TF_DT) {
-                for (int pass = 0; pass < kPasses; ++pass) {
-                    // term 0: a_hi b_hi, term 1: a_hi b_lo, term 2: a_lo b_hi.  The loops over terms are
-                    // NOT unrolled and descriptors are base + offset: fully unrolled, the 72 descriptors
-                    // become loop invariants that spill (the issuing thread then waits on local memory
-                    // for every MMA: 280 cycles per instruction instead of 50).
-                    wait_ops();   // X operand ready: Q|K|V = X Wqkv^T
+            // D[., n0 .. n0 + N) (+)= X operand (K = 64) x rows [n0, n0 + N) of Wqkv, three split terms.
+            // term 0: a_hi b_hi, term 1: a_hi b_lo, term 2: a_lo b_hi.  The loops over terms are NOT
+            // unrolled and descriptors are base + offset: fully unrolled, the 72 descriptors of a pass
+            // become loop invariants that spill (the issuing thread then waits on local memory for
+            // every MMA: 280 cycles per instruction instead of 50).
+            auto project = [&](uint32_t n0, uint32_t idesc) {
 #pragma unroll 1
-                    for (int term = 0; term < 3; ++term) {
-                        const uint32_t a = ts + (term == 2 ? 224 : 192);
-                        const uint64_t b = d_qkv + (term == 1 ? 24576 / 16 : 0);
+                for (int term = 0; term < 3; ++term) {
+                    const uint32_t a = ts + (term == 2 ? 224 : 192);
+                    const uint64_t b = d_qkv + (term == 1 ? 24576 / 16 : 0) + n0 * (128 / 16);
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) umma_bf16_ts(ts, a + 8 * k, b + 2 * k, id192, (term | k) != 0);
+                    for (int k = 0; k < 4; ++k) umma_bf16_ts(ts + n0, a + 8 * k, b + 2 * k, idesc, (term | k) != 0);
+                }
+                umma_commit(&ctl->to_epi[slot]);
+            };
+            mbar_wait(&ctl->w_full, 0);
+            for (int item = blockIdx.x * 2 + slot; item < items; item += 2 * gridDim.x) {
+                for (int pass = 0; pass < kPasses; ++pass) {
+                    if (kCross) {
+                        wait_ops(); project(64, id128);    // source rows in the operand: K | V
+                        wait_ops(); project(0, id64);      // query rows in the operand: Q
+                    } else {
+                        wait_ops(); project(0, id192);     // Q | K | V
                     }
-                    umma_commit(&ctl->to_epi[slot]);
                     wait_ops();   // message ready: merge
 #pragma unroll 1
                     for (int term = 0; term < 3; ++term) {
@@ -293,84 +278,87 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     umma_commit(&ctl->to_epi[slot]);
                 }
             }
-#ifdef FM_TF_PHASE_CLOCK
-            if (blockIdx.x == 0) printf("mma warp %d: wait %lld %lld %lld %lld  issue %lld %lld %lld %lld\n", warp, mw[0], mw[1], mw[2], mw[3], mi[0], mi[1], mi[2], mi[3]);
-#endif
         }
     } else {
         // ------------------------------------------------------------------ epilogue warps
-        reg_alloc<104>();   // pool = 640 x 96 (launch) - 128 x 40 (control warps) = 512 x 110
+        reg_alloc<104>();   // pool = 640 x 96 (launch) - 128 x 56 (control warps) = 512 x 106
         const int slot = warp >> 3, g = (warp >> 2) & 1, q = warp & 3;
         const int st = threadIdx.x & (kSlotThreads - 1);          // thread within the slot
-        const int w = q >> 1, r = (q & 1) * 32 + lane;            // window, window cell
+        const int w = q >> 1, r = (q & 1) * 32 + lane;            // window slot of the tile, window cell
         const int row = q * 32 + lane;                             // TMEM lane
-        const bool valid = r < WW;
         const uint32_t tl = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + slot * kSlotCols;
         const uint32_t bar_id = 1 + slot;
         const float* ln = reinterpret_cast<const float*>(blob + kOffLn) + 32 * g;
         float2* lnrow = lnx + (slot * 128 + row) * 2;
+        float* kvm = kvm_all + slot * 2 * 64 * 8;                  // this slot's KV matrices / key sums
+        float* ksum = ksum_all + slot * 2 * 64;
         uint32_t it = 0;
-        auto wait_acc = [&]() { mbar_wait_backoff<TF_SLEEP>(&ctl->to_epi[slot], it & 1); ++it; tc_fence_after(); };
+        auto wait_acc = [&]() { mbar_wait_backoff<64>(&ctl->to_epi[slot], it & 1); ++it; tc_fence_after(); };
         auto signal_mma = [&]() {
             tmem_st_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&ctl->to_mma[slot]);
         };
-        mbar_wait(&ctl->w_full, 0);   // LayerNorm parameters live in the blob
-#ifdef FM_TF_PHASE_CLOCK
-        long long pc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, pt = clock64();
-#define TF_TICK(k) { const long long now_ = clock64(); pc[k] += now_ - pt; pt = now_; }
-#elif defined(FM_TF_TRACE)
-        int tile_no = 0;
-#define TF_TICK(k) { if (blockIdx.x == 0 && warp == 0 && lane == 0 && tile_no == 3) g_trace[k] = clock64(); }
-#else
-#define TF_TICK(k)
-#endif
-
-        for (int t = TF_T0; t < M; t += TF_DT) {
-            float x[32];
-            {
-                const float4* src = reinterpret_cast<const float4*>(p.in[w] + (static_cast<size_t>(t) * WW + (valid ? r : 0)) * kC + 32 * g);
+        // this thread's 32 channels of (side, match m, cell r); zeros for padding lanes / matches
+        auto load_rows = [&](float (&dst)[32], int side, int m) {
+            const bool ok = r < WW && m < M;
+            const float4* src = reinterpret_cast<const float4*>(p.in[side] + (static_cast<size_t>(ok ? m : 0) * WW + (ok ? r : 0)) * kC + 32 * g);
 #pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    const float4 v = valid ? __ldg(src + c) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
-                }
+            for (int c = 0; c < 8; ++c) {
+                const float4 v = ok ? __ldg(src + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+                dst[4 * c] = v.x; dst[4 * c + 1] = v.y; dst[4 * c + 2] = v.z; dst[4 * c + 3] = v.w;
             }
-            store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
-            signal_mma();
-            if (valid && t + TF_DT < M)   // this thread's 128 bytes of the slot's next tile -> L2
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(p.in[w] + (static_cast<size_t>(t + TF_DT) * WW + r) * kC + 32 * g));
-            TF_TICK(0)
+        };
+        auto prefetch_rows = [&](int side, int m) {
+            if (r < WW && m < M)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(p.in[side] + (static_cast<size_t>(m) * WW + r) * kC + 32 * g));
+        };
+        mbar_wait(&ctl->w_full, 0);   // LayerNorm parameters live in the blob
+
+        for (int item = blockIdx.x * 2 + slot; item < items; item += 2 * gridDim.x) {
+            const int next = item + 2 * gridDim.x;
+            // match of this thread's row; self: both windows of one match, cross: same side of two matches
+            const int m = kCross ? 2 * item + w : item;
+            const bool valid = r < WW && m < M;
+            float x[32];
+            if (kCross) {
+                load_rows(x, 1, m);                                   // the image-1 windows: K | V source of pass 0
+                store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
+                signal_mma();
+                load_rows(x, 0, m);                                   // in flight under the K | V phase
+                if (next < items) { prefetch_rows(1, 2 * next + w); prefetch_rows(0, 2 * next + w); }
+            } else {
+                load_rows(x, w, m);
+                store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
+                signal_mma();
+                if (next < items) prefetch_rows(w, next);
+            }
 
 #pragma unroll 1
             for (int pass = 0; pass < kPasses; ++pass) {
-                const bool active = !kCross || w == pass;     // this row is a query row / gets updated
-                const bool is_src = !kCross || w != pass;     // this row supplies keys and values
-                const int srcw = kCross ? (w ^ 1) : w;
-                // ================= attention: Q, K, V -> message =================
-                wait_acc();
-                TF_TICK(1)
+                // ================= attention: K, V -> per-window KV matrices =================
+                wait_acc();   // self: Q | K | V ready; cross: K | V of the source rows ready
                 float qf[32];
                 uint32_t v[32];
-                if (active) {
+                if (!kCross) {   // Q first: its conversion overlaps the wait for the scratch lock
                     tmem_ld_32x32(tl + 32 * g, v);
                     tmem_ld_wait();
 #pragma unroll
                     for (int i = 0; i < 32; ++i) qf[i] = elu1(__uint_as_float(v[i]));
                 }
-                if (st == 0) {   // the K | V scratch is shared by the two slots
-                    while (atomicCAS(&ctl->lock_owner, 0, slot + 1) != 0) __nanosleep(64);
+                // The K | V scratch is shared by the two slots: held until this slot's K^T V sums are
+                // done (every warp signs off after its last scratch read).
+                if (st == 0) {
+                    while (atomicCAS(&ctl->lock_owner, 0, slot + 1) != 0) __nanosleep(32);
                     ctl->lock_left = 8;
                 }
                 named_bar_sync(bar_id, kSlotThreads);
-                TF_TICK(2)
-                if (is_src) {
-                    uint8_t* rowp = scr + (w * kMaxWW + (valid ? r : 0)) * kScrRow;
+                {
+                    uint8_t* rowp = scr + (w * kMaxWW + (r < WW ? r : 0)) * kScrRow;
                     tmem_ld_32x32(tl + 64 + 32 * g, v);
                     tmem_ld_wait();
-                    if (valid) {
+                    if (r < WW) {
 #pragma unroll
                         for (int c = 0; c < 8; ++c)
                             *reinterpret_cast<float4*>(rowp + ((8 * g + c) << 4)) =
@@ -379,7 +367,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     }
                     tmem_ld_32x32(tl + 128 + 32 * g, v);
                     tmem_ld_wait();
-                    if (valid) {
+                    if (r < WW) {
 #pragma unroll
                         for (int c = 0; c < 8; ++c)
                             *reinterpret_cast<uint4*>(rowp + ((16 + 8 * g + c) << 4)) =
@@ -387,157 +375,125 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     }
                 }
                 named_bar_sync(bar_id, kSlotThreads);
-                TF_TICK(3)
                 {   // KV[d][v] = sum_r K[r][d] V[r][v] within a head; thread = (window, d, half of the 8 v)
                     const int w2 = st >> 7, d = (st & 127) >> 1, vh = st & 1;
-                    if (!kCross || w2 != pass) {
-                        const uint8_t* kp = scr + w2 * kMaxWW * kScrRow + d * 4;
-                        const uint8_t* vp = scr + w2 * kMaxWW * kScrRow + 256 + (d >> 3) * 32 + vh * 16;
-                        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, ks = 0.f;
+                    const uint8_t* kp = scr + w2 * kMaxWW * kScrRow + d * 4;
+                    const uint8_t* vp = scr + w2 * kMaxWW * kScrRow + 256 + (d >> 3) * 32 + vh * 16;
+                    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, ks = 0.f;
 #pragma unroll
-                        for (int rr = 0; rr < kMaxWW; ++rr) {
-                            if (kWW ? rr < kWW : rr < WW) {
-                                const float kv = *reinterpret_cast<const float*>(kp + rr * kScrRow);
-                                const float4 vv = *reinterpret_cast<const float4*>(vp + rr * kScrRow);
-                                a0 = fmaf(kv, vv.x, a0); a1 = fmaf(kv, vv.y, a1);
-                                a2 = fmaf(kv, vv.z, a2); a3 = fmaf(kv, vv.w, a3);
-                                ks += kv;
-                            }
+                    for (int rr = 0; rr < kMaxWW; ++rr) {
+                        if (kWW ? rr < kWW : rr < WW) {
+                            const float kv = *reinterpret_cast<const float*>(kp + rr * kScrRow);
+                            const float4 vv = *reinterpret_cast<const float4*>(vp + rr * kScrRow);
+                            a0 = fmaf(kv, vv.x, a0); a1 = fmaf(kv, vv.y, a1);
+                            a2 = fmaf(kv, vv.z, a2); a3 = fmaf(kv, vv.w, a3);
+                            ks += kv;
                         }
-                        *reinterpret_cast<float4*>(kvm + (w2 * 64 + d) * 8 + vh * 4) = make_float4(a0, a1, a2, a3);
-                        if (vh == 0) ksum[w2 * 64 + d] = ks;
                     }
+                    *reinterpret_cast<float4*>(kvm + (w2 * 64 + d) * 8 + vh * 4) = make_float4(a0, a1, a2, a3);
+                    if (vh == 0) ksum[w2 * 64 + d] = ks;
                 }
-                named_bar_sync(bar_id, kSlotThreads);
-                TF_TICK(4)
-                if (active) {
-#pragma unroll
-                    for (int hh = 0; hh < 4; ++hh) {
-                        const int h = 4 * g + hh;
-                        const float* kvp = kvm + (srcw * 64 + h * 8) * 8;
-                        const float* ksp = ksum + srcw * 64 + h * 8;
-                        float den = 1e-6f, m[8];
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) m[j] = 0.f;
-#pragma unroll
-                        for (int dd = 0; dd < 8; ++dd) {
-                            const float qd = qf[hh * 8 + dd];
-                            const float4 ka = *reinterpret_cast<const float4*>(kvp + dd * 8);
-                            const float4 kb = *reinterpret_cast<const float4*>(kvp + dd * 8 + 4);
-                            den = fmaf(qd, ksp[dd], den);
-                            m[0] = fmaf(qd, ka.x, m[0]); m[1] = fmaf(qd, ka.y, m[1]);
-                            m[2] = fmaf(qd, ka.z, m[2]); m[3] = fmaf(qd, ka.w, m[3]);
-                            m[4] = fmaf(qd, kb.x, m[4]); m[5] = fmaf(qd, kb.y, m[5]);
-                            m[6] = fmaf(qd, kb.z, m[6]); m[7] = fmaf(qd, kb.w, m[7]);
-                        }
-                        const float z = 1.0f / den;
-                        uint32_t hi[4], lo[4];
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) split2(m[2 * j] * z, m[2 * j + 1] * z, hi[j], lo[j]);
-                        tmem_st_32x4(tl + 128 + 16 * g + 4 * hh, hi);
-                        tmem_st_32x4(tl + 160 + 16 * g + 4 * hh, lo);
-                    }
-                }
-                tmem_st_wait();
-                tc_fence_before();
                 __syncwarp();
-                if (lane == 0) {
+                if (lane == 0) {   // this warp is done with the shared scratch
                     __threadfence_block();
                     if (atomicSub(&ctl->lock_left, 1) == 1) atomicExch(&ctl->lock_owner, 0);
-                    mbar_arrive(&ctl->to_mma[slot]);
                 }
-                TF_TICK(5)
+                if (kCross) {
+                    // the rows to update take the tile: their operand -> Q projection
+                    store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
+                    signal_mma();
+                    wait_acc();
+                    tmem_ld_32x32(tl + 32 * g, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) qf[i] = elu1(__uint_as_float(v[i]));
+                }
+                named_bar_sync(bar_id, kSlotThreads);   // KV matrices visible
+                // ================= message = (Q KV) / (Q sum K + eps)  (attentions.py:42-44) =================
+#pragma unroll
+                for (int hh = 0; hh < 4; ++hh) {
+                    const int h = 4 * g + hh;
+                    const float* kvp = kvm + (w * 64 + h * 8) * 8;
+                    const float* ksp = ksum + w * 64 + h * 8;
+                    float den = 1e-6f, mm[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) mm[j] = 0.f;
+#pragma unroll
+                    for (int dd = 0; dd < 8; ++dd) {
+                        const float qd = qf[hh * 8 + dd];
+                        const float4 ka = *reinterpret_cast<const float4*>(kvp + dd * 8);
+                        const float4 kb = *reinterpret_cast<const float4*>(kvp + dd * 8 + 4);
+                        den = fmaf(qd, ksp[dd], den);
+                        mm[0] = fmaf(qd, ka.x, mm[0]); mm[1] = fmaf(qd, ka.y, mm[1]);
+                        mm[2] = fmaf(qd, ka.z, mm[2]); mm[3] = fmaf(qd, ka.w, mm[3]);
+                        mm[4] = fmaf(qd, kb.x, mm[4]); mm[5] = fmaf(qd, kb.y, mm[5]);
+                        mm[6] = fmaf(qd, kb.z, mm[6]); mm[7] = fmaf(qd, kb.w, mm[7]);
+                    }
+                    const float z = 1.0f / den;
+                    uint32_t hi[4], lo[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) split2(mm[2 * j] * z, mm[2 * j + 1] * z, hi[j], lo[j]);
+                    tmem_st_32x4(tl + 128 + 16 * g + 4 * hh, hi);
+                    tmem_st_32x4(tl + 160 + 16 * g + 4 * hh, lo);
+                }
+                signal_mma();
                 // ================= merge -> LayerNorm 1 =================
                 wait_acc();
-                TF_TICK(6)
                 float y[32];
-                float2 mine = make_float2(0.f, 0.f);
-                if (active) {
-                    tmem_ld_32x32(tl + 32 * g, v);
-                    tmem_ld_wait();
+                tmem_ld_32x32(tl + 32 * g, v);
+                tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) y[i] = __uint_as_float(v[i]);
-                    mine = local_stats(y);
-                    lnrow[g] = mine;
-                }
+                for (int i = 0; i < 32; ++i) y[i] = __uint_as_float(v[i]);
+                float2 mine = local_stats(y);
+                lnrow[g] = mine;
                 named_bar_sync(bar_id, kSlotThreads);
-                if (active) {
-                    layer_norm32(y, mine, lnrow[g ^ 1], ln, ln + 64);
-                    store_operand32(tl + 128 + 16 * g, tl + 160 + 16 * g, y);
-                }
+                layer_norm32(y, mine, lnrow[g ^ 1], ln, ln + 64);
+                store_operand32(tl + 128 + 16 * g, tl + 160 + 16 * g, y);
                 signal_mma();
-                TF_TICK(7)
                 // ================= MLP hidden: relu =================
                 wait_acc();
-                TF_TICK(8)
-                if (active) {
 #pragma unroll
-                    for (int half = 0; half < 2; ++half) {
-                        tmem_ld_32x32(tl + 64 * g + 32 * half, v);
-                        tmem_ld_wait();
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) y[i] = fmaxf(__uint_as_float(v[i]), 0.f);
-                        store_operand32(tl + 192 + 32 * g + 16 * half, tl + 128 + 32 * g + 16 * half, y);
-                    }
-                }
-                signal_mma();
-                TF_TICK(9)
-                // ================= MLP out -> LayerNorm 2 -> residual =================
-                wait_acc();
-                TF_TICK(10)
-                if (active) {
-                    tmem_ld_32x32(tl + 32 * g, v);
+                for (int half = 0; half < 2; ++half) {
+                    tmem_ld_32x32(tl + 64 * g + 32 * half, v);
                     tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) y[i] = __uint_as_float(v[i]);
-                    mine = local_stats(y);
-                    lnrow[g] = mine;
+                    for (int i = 0; i < 32; ++i) y[i] = fmaxf(__uint_as_float(v[i]), 0.f);
+                    store_operand32(tl + 192 + 32 * g + 16 * half, tl + 128 + 32 * g + 16 * half, y);
                 }
-                named_bar_sync(bar_id, kSlotThreads);
-                if (active) {
-                    layer_norm32(y, mine, lnrow[g ^ 1], ln + 128, ln + 192);
+                signal_mma();
+                // ================= MLP out -> LayerNorm 2 -> residual =================
+                wait_acc();
+                tmem_ld_32x32(tl + 32 * g, v);
+                tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) x[i] += y[i];
-                }
-                if (pass + 1 < kPasses) {
-                    // the hidden activations overwrote this row's X operand: put the new x back
-                    if (active) store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
+                for (int i = 0; i < 32; ++i) y[i] = __uint_as_float(v[i]);
+                mine = local_stats(y);
+                lnrow[g] = mine;
+                named_bar_sync(bar_id, kSlotThreads);
+                layer_norm32(y, mine, lnrow[g ^ 1], ln + 128, ln + 192);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) x[i] += y[i];
+                if (kCross && pass == 0) {
+                    // the updated image-0 windows are the K | V source of pass 1 (transformer.py:95)
+                    store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
                     signal_mma();
                 }
-            }
-            if (valid) {
-                float4* dst = reinterpret_cast<float4*>(p.out[w] + (static_cast<size_t>(t) * WW + r) * kC + 32 * g);
+                if (valid) {
+                    float4* dst = reinterpret_cast<float4*>(p.out[kCross ? pass : w] + (static_cast<size_t>(m) * WW + r) * kC + 32 * g);
 #pragma unroll
-                for (int c = 0; c < 8; ++c) dst[c] = make_float4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
+                    for (int c = 0; c < 8; ++c) dst[c] = make_float4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
+                }
+                if (kCross && pass == 0) load_rows(x, 1, m);   // pass 1 updates the image-1 windows
             }
-            TF_TICK(11)
-#ifdef FM_TF_TRACE
-            ++tile_no;
-#endif
         }
-#ifdef FM_TF_PHASE_CLOCK
-        if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 13))
-            printf("warp %d cycles: load %lld | waitQKV %lld lock %lld kvstore %lld kvsum %lld msg %lld | waitMerge %lld ln1 %lld | waitHid %lld relu %lld | waitOut %lld ln2+store %lld\n",
-                   warp, pc[0], pc[1], pc[2], pc[3], pc[4], pc[5], pc[6], pc[7], pc[8], pc[9], pc[10], pc[11]);
-#endif
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-#ifdef FM_TF_TRACE
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        const long long t0 = g_trace[0];
-        printf("epi : opsX %lld | accQKV %lld lock %lld kvst %lld kvsum %lld msgdone %lld | accMerge %lld ln1done %lld | accHid %lld reludone %lld | accOut %lld end %lld\n",
-               0ll, g_trace[1] - t0, g_trace[2] - t0, g_trace[3] - t0, g_trace[4] - t0, g_trace[5] - t0, g_trace[6] - t0, g_trace[7] - t0,
-               g_trace[8] - t0, g_trace[9] - t0, g_trace[10] - t0, g_trace[11] - t0);
-        printf("mma : seenX %lld issuedQKV %lld | seenMsg %lld issuedMerge %lld | seenLn1 %lld issuedMlp1 %lld | seenRelu %lld issuedMlp2 %lld\n",
-               g_trace[16] - t0, g_trace[17] - t0, g_trace[18] - t0, g_trace[19] - t0, g_trace[20] - t0, g_trace[21] - t0, g_trace[22] - t0, g_trace[23] - t0);
-    }
-#endif
     if (warp == 18) tmem_dealloc<512>(tmem_base);
 }
 
-constexpr size_t kTfSmem = 1024 + kBlobBytes + kScratchBytes + 2 * 64 * 8 * 4 + 2 * 64 * 4 + 2 * 128 * 2 * 8 + sizeof(TfCtl);
+constexpr size_t kTfSmem = 1024 + kBlobBytes + kScratchBytes + 2 * (2 * 64 * 8 * 4 + 2 * 64 * 4) + 2 * 128 * 2 * 8 + sizeof(TfCtl);
 static_assert(kTfSmem <= 232448, "fine transformer shared memory budget");
 
 }  // namespace
