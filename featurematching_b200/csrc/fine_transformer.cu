@@ -303,11 +303,13 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
         // this thread's 32 channels of (side, match m, cell r); zeros for padding lanes / matches
         auto load_rows = [&](float (&dst)[32], int side, int m) {
             const bool ok = r < WW && m < M;
-            const float4* src = reinterpret_cast<const float4*>(p.in[side] + (static_cast<size_t>(ok ? m : 0) * WW + (ok ? r : 0)) * kC + 32 * g);
+            const float* src = p.in[side] + (static_cast<size_t>(ok ? m : 0) * WW + (ok ? r : 0)) * kC + 32 * g;
+            if (ok) {
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const float4 v = ok ? __ldg(src + c) : make_float4(0.f, 0.f, 0.f, 0.f);
-                dst[4 * c] = v.x; dst[4 * c + 1] = v.y; dst[4 * c + 2] = v.z; dst[4 * c + 3] = v.w;
+                for (int c = 0; c < 4; ++c) ldg256(src, dst, 8 * c);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) dst[i] = 0.f;
             }
         };
         auto prefetch_rows = [&](int side, int m) {
@@ -478,10 +480,10 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
                     signal_mma();
                 }
-                if (valid) {
-                    float4* dst = reinterpret_cast<float4*>(p.out[kCross ? pass : w] + (static_cast<size_t>(m) * WW + r) * kC + 32 * g);
+                if (valid) {   // four full 32-byte sectors per thread
+                    float* dst = p.out[kCross ? pass : w] + (static_cast<size_t>(m) * WW + r) * kC + 32 * g;
 #pragma unroll
-                    for (int c = 0; c < 8; ++c) dst[c] = make_float4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
+                    for (int c = 0; c < 4; ++c) stg256(dst, x, 8 * c);
                 }
                 if (kCross && pass == 0) load_rows(x, 1, m);   // pass 1 updates the image-1 windows
             }

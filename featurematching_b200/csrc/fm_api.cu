@@ -454,8 +454,8 @@ int fm_fine_transformer(const float* win0, const float* win1, const int32_t* cou
             if (!layer_params[10 * l + k]) { set_error("layer_params[%d] is NULL", 10 * l + k); return FM_ERR_BAD_ARG; }
     }
     if ((reinterpret_cast<uintptr_t>(win0) | reinterpret_cast<uintptr_t>(win1) | reinterpret_cast<uintptr_t>(out0) |
-         reinterpret_cast<uintptr_t>(out1) | reinterpret_cast<uintptr_t>(workspace)) & 15) {
-        set_error("window and workspace pointers must be 16-byte aligned");
+         reinterpret_cast<uintptr_t>(out1) | reinterpret_cast<uintptr_t>(workspace)) & 31) {
+        set_error("window and workspace pointers must be 32-byte aligned");
         return FM_ERR_BAD_ARG;
     }
     if (workspace_bytes < fine_transformer_workspace_bytes(n_layers)) {

@@ -307,4 +307,20 @@ __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, u
         : "memory");
 }
 
+// ------------------------------------------------------------------ 256-bit global accesses (sm_100)
+// A thread that owns 128 contiguous bytes moves them as four full 32-byte sectors instead of eight
+// half sectors (row-strided 16-byte stores reach L2 as partial-sector writes).
+__device__ __forceinline__ void ldg256(const float* p, float (&v)[32], int i) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[i]), "=f"(v[i + 1]), "=f"(v[i + 2]), "=f"(v[i + 3]), "=f"(v[i + 4]), "=f"(v[i + 5]),
+                   "=f"(v[i + 6]), "=f"(v[i + 7])
+                 : "l"(p + i));
+}
+__device__ __forceinline__ void stg256(float* p, const float (&v)[32], int i) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 ::"l"(p + i), "f"(v[i]), "f"(v[i + 1]), "f"(v[i + 2]), "f"(v[i + 3]), "f"(v[i + 4]), "f"(v[i + 5]),
+                   "f"(v[i + 6]), "f"(v[i + 7])
+                 : "memory");
+}
+
 }  // namespace fm

@@ -160,7 +160,8 @@ FM_API int fm_fine_match(const void* win0, const void* win1, int win_dtype, cons
  * layer_params: HOST array [n_layers * 10] of DEVICE pointers to the fp32 parameters of each
  *   layer in state-dict order q_proj.weight [C,C], k_proj.weight, v_proj.weight, merge.weight,
  *   mlp.0.weight [2C,2C], mlp.2.weight [C,2C], norm1.weight [C], norm1.bias, norm2.weight, norm2.bias.
- * workspace: fm_fine_transformer_workspace_bytes(n_layers) bytes, 16-byte aligned (packed weights).
+ * workspace: fm_fine_transformer_workspace_bytes(n_layers) bytes (packed weights); windows, outputs and
+ * workspace must be 32-byte aligned (256-bit global accesses).
  * All GEMMs run on the tensor cores with fp32-grade 3-term bf16 splits; entries >= *count are
  * not touched. */
 FM_API size_t fm_fine_transformer_workspace_bytes(int n_layers);
