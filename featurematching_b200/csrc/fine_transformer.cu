@@ -149,6 +149,7 @@ struct __align__(16) TfCtl {
     uint64_t w_full;
     uint64_t to_epi[2];     // MMA warp -> the slot's epilogue warps (tcgen05.commit)
     uint64_t to_mma[2];     // epilogue warps -> the slot's MMA warp (8 arrivals)
+    uint64_t q_done[2];     // cross: Q projection complete (own barrier, own phase counter)
     uint32_t tmem_base;
     int lock_owner;         // attention scratch: 0 free, else slot + 1
     int lock_left;          // warps of the owner still using it
@@ -191,7 +192,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
 
     if (threadIdx.x == 0) {
         mbar_init(&ctl->w_full, 1);
-        for (int s = 0; s < 2; ++s) { mbar_init(&ctl->to_epi[s], 1); mbar_init(&ctl->to_mma[s], 8); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&ctl->to_epi[s], 1); mbar_init(&ctl->to_mma[s], 8); mbar_init(&ctl->q_done[s], 1); }
         ctl->lock_owner = 0;
         ctl->lock_left = 0;
         fence_mbar_init();
@@ -226,7 +227,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
             // unrolled and descriptors are base + offset: fully unrolled, the 72 descriptors of a pass
             // become loop invariants that spill (the issuing thread then waits on local memory for
             // every MMA: 280 cycles per instruction instead of 50).
-            auto project = [&](uint32_t n0, uint32_t idesc) {
+            auto project = [&](uint32_t n0, uint32_t idesc, uint64_t* done) {
 #pragma unroll 1
                 for (int term = 0; term < 3; ++term) {
                     const uint32_t a = ts + (term == 2 ? 224 : 192);
@@ -234,16 +235,18 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
 #pragma unroll
                     for (int k = 0; k < 4; ++k) umma_bf16_ts(ts + n0, a + 8 * k, b + 2 * k, idesc, (term | k) != 0);
                 }
-                umma_commit(&ctl->to_epi[slot]);
+                umma_commit(done);
             };
             mbar_wait(&ctl->w_full, 0);
             for (int item = blockIdx.x * 2 + slot; item < items; item += 2 * gridDim.x) {
                 for (int pass = 0; pass < kPasses; ++pass) {
                     if (kCross) {
-                        wait_ops(); project(64, id128);    // source rows in the operand: K | V
-                        wait_ops(); project(0, id64);      // query rows in the operand: Q
+                        // K | V of the source rows, then -- after the operand swap -- Q of the rows to
+                        // update: the Q batch runs while the epilogue reduces K^T V
+                        wait_ops(); project(64, id128, &ctl->to_epi[slot]);
+                        wait_ops(); project(0, id64, &ctl->q_done[slot]);
                     } else {
-                        wait_ops(); project(0, id192);     // Q | K | V
+                        wait_ops(); project(0, id192, &ctl->to_epi[slot]);   // Q | K | V
                     }
                     wait_ops();   // message ready: merge
 #pragma unroll 1
@@ -292,7 +295,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
         float2* lnrow = lnx + (slot * 128 + row) * 2;
         float* kvm = kvm_all + slot * 2 * 64 * 8;                  // this slot's KV matrices / key sums
         float* ksum = ksum_all + slot * 2 * 64;
-        uint32_t it = 0;
+        uint32_t it = 0, itq = 0;
         auto wait_acc = [&]() { mbar_wait_backoff<64>(&ctl->to_epi[slot], it & 1); ++it; tc_fence_after(); };
         auto signal_mma = [&]() {
             tmem_st_wait();
@@ -340,7 +343,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
 #pragma unroll 1
             for (int pass = 0; pass < kPasses; ++pass) {
                 // ================= attention: K, V -> per-window KV matrices =================
-                wait_acc();   // self: Q | K | V ready; cross: K | V of the source rows ready
+                wait_acc();   // self: Q | K | V ready; cross: K | V of the source rows
                 float qf[32];
                 uint32_t v[32];
                 if (!kCross) {   // Q first: its conversion overlaps the wait for the scratch lock
@@ -348,6 +351,11 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     tmem_ld_wait();
 #pragma unroll
                     for (int i = 0; i < 32; ++i) qf[i] = elu1(__uint_as_float(v[i]));
+                } else {
+                    // K | V of the source rows are in the accumulators, their operand is free: the rows
+                    // to update take the tile now, and their Q projection runs under the K^T V phase
+                    store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
+                    signal_mma();
                 }
                 // The K | V scratch is shared by the two slots: held until this slot's K^T V sums are
                 // done (every warp signs off after its last scratch read).
@@ -401,10 +409,9 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     if (atomicSub(&ctl->lock_left, 1) == 1) atomicExch(&ctl->lock_owner, 0);
                 }
                 if (kCross) {
-                    // the rows to update take the tile: their operand -> Q projection
-                    store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
-                    signal_mma();
-                    wait_acc();
+                    mbar_wait_backoff<64>(&ctl->q_done[slot], itq & 1);   // Q (ran under the K^T V phase)
+                    ++itq;
+                    tc_fence_after();
                     tmem_ld_32x32(tl + 32 * g, v);
                     tmem_ld_wait();
 #pragma unroll
