@@ -65,31 +65,32 @@ __device__ __forceinline__ void put_split(uint8_t* tile_hi, uint8_t* tile_lo, in
     *reinterpret_cast<__nv_bfloat16*>(tile_lo + off) = l;
 }
 
-// one block per layer
+// one layer per launch, grid-stride over its 40 960 weights
 __global__ void __launch_bounds__(256) tf_pack_kernel(TfLayerParams p, uint8_t* __restrict__ blob) {
-    for (int e = threadIdx.x; e < 192 * 64; e += blockDim.x) {
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
+    for (int e = tid; e < 192 * 64; e += nthr) {
         const int n = e >> 6, kk = e & 63;
         const float* src = n < 64 ? p.q : (n < 128 ? p.k : p.v);
         put_split(blob + kOffQkv, blob + kOffQkv + 24576, n, kk, src[(n & 63) * 64 + kk]);
     }
-    for (int e = threadIdx.x; e < 64 * 64; e += blockDim.x) {
+    for (int e = tid; e < 64 * 64; e += nthr) {
         const int n = e >> 6, kk = e & 63;
         put_split(blob + kOffMerge, blob + kOffMerge + 8192, n, kk, p.merge[e]);
     }
-    for (int e = threadIdx.x; e < 128 * 128; e += blockDim.x) {
+    for (int e = tid; e < 128 * 128; e += nthr) {
         const int n = e >> 7, k = e & 127, kc = k >> 6;
         put_split(blob + kOffMlp0 + kc * 16384, blob + kOffMlp0 + (2 + kc) * 16384, n, k & 63, p.mlp0[e]);
     }
-    for (int e = threadIdx.x; e < 64 * 128; e += blockDim.x) {
+    for (int e = tid; e < 64 * 128; e += nthr) {
         const int n = e >> 7, k = e & 127, kc = k >> 6;
         put_split(blob + kOffMlp2 + kc * 8192, blob + kOffMlp2 + (2 + kc) * 8192, n, k & 63, p.mlp2[e]);
     }
     float* ln = reinterpret_cast<float*>(blob + kOffLn);
-    if (threadIdx.x < 64) {
-        ln[threadIdx.x] = p.n1w[threadIdx.x];
-        ln[64 + threadIdx.x] = p.n1b[threadIdx.x];
-        ln[128 + threadIdx.x] = p.n2w[threadIdx.x];
-        ln[192 + threadIdx.x] = p.n2b[threadIdx.x];
+    if (tid < 64) {
+        ln[tid] = p.n1w[tid];
+        ln[64 + tid] = p.n1b[tid];
+        ln[128 + tid] = p.n2w[tid];
+        ln[192 + tid] = p.n2b[tid];
     }
 }
 
@@ -520,7 +521,7 @@ cudaError_t launch_fine_transformer(const float* win0, const float* win1, const 
     for (int l = 0; l < n_layers; ++l) {
         const float* const* q = layer_ptrs + 10 * l;
         TfLayerParams lp{q[0], q[1], q[2], q[3], q[4], q[5], q[6], q[7], q[8], q[9]};
-        tf_pack_kernel<<<1, 256, 0, st>>>(lp, blobs + static_cast<size_t>(l) * kBlobBytes);
+        tf_pack_kernel<<<20, 256, 0, st>>>(lp, blobs + static_cast<size_t>(l) * kBlobBytes);
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
