@@ -361,7 +361,11 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                 // The K | V scratch is shared by the two slots: held until this slot's K^T V sums are
                 // done (every warp signs off after its last scratch read).
                 if (st == 0) {
-                    while (atomicCAS(&ctl->lock_owner, 0, slot + 1) != 0) __nanosleep(32);
+                    uint32_t spins = 0;
+                    while (atomicCAS(&ctl->lock_owner, 0, slot + 1) != 0) {
+                        __nanosleep(32);
+                        if (++spins > 40000000u) __trap();   // protocol bug -> launch failure, not a hung GPU
+                    }
                     ctl->lock_left = 8;
                 }
                 named_bar_sync(bar_id, kSlotThreads);

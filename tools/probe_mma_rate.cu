@@ -5,6 +5,20 @@
 #include "../featurematching_b200/csrc/fm_ptx.cuh"
 using namespace fm;
 
+// same batch, accumulating alternately into two independent regions (D0 at column 0, D1 at column 64)
+template <int N>
+__device__ long long run_alt(uint32_t tm, uint32_t sbase, uint64_t* bar, uint32_t& ph, int n) {
+    constexpr uint32_t idesc = umma_idesc_bf16_f32(128, N);
+    long long t0 = clock64();
+    for (int i = 0; i < n; ++i) {
+        const int k = i & 3;
+        umma_bf16_ts(tm + 64 * (i & 1), tm + 256 + 8 * (i & 7), umma_desc_k_sw128(sbase + 32 * k), idesc, i > 1 ? 1u : 0u);
+    }
+    umma_commit(bar);
+    mbar_wait(bar, ph); ph ^= 1;
+    return clock64() - t0;
+}
+
 template <int N, bool TS>
 __device__ long long run(uint32_t tm, uint32_t sbase, uint64_t* bar, uint32_t& ph, int n) {
     constexpr uint32_t idesc = umma_idesc_bf16_f32(128, N);
@@ -51,6 +65,8 @@ __global__ void __launch_bounds__(640, 1) probe(long long* out, int pollers) {
             out[o++] = run<192, false>(tm, sb, &bar, ph, 12);
             out[o++] = run<64, true>(tm, sb, &bar, ph, 1);
             out[o++] = run<64, true>(tm, sb, &bar, ph, 96);
+            out[o++] = run_alt<64>(tm, sb, &bar, ph, 24);
+            out[o++] = run_alt<64>(tm, sb, &bar, ph, 12);
         }
         done = 1;
         mbar_arrive(&bar2);
@@ -66,14 +82,14 @@ __global__ void __launch_bounds__(640, 1) probe(long long* out, int pollers) {
 int main() {
     long long* d; cudaMalloc(&d, 16 * 8);
     cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 66560);
-    for (int pollers = 0; pollers <= 16; pollers += 8) {
+    for (int pollers = 0; pollers <= 0; pollers += 8) {
     probe<<<1, 640, 66560>>>(d, pollers);
     printf("launch: %s\n", cudaGetErrorString(cudaDeviceSynchronize()));
     long long h[16]; cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
     const char* names[] = {"TS N=64 x12", "TS N=64 x24", "TS N=128 x24", "TS N=192 x12", "SS N=64 x12", "SS N=64 x24",
-                           "SS N=128 x24", "SS N=192 x12", "TS N=64 x1", "TS N=64 x96"};
+                           "SS N=128 x24", "SS N=192 x12", "TS N=64 x1", "TS N=64 x96", "TS N=64 x24 2 accumulators", "TS N=64 x12 2 accumulators"};
     printf("pollers = %d\n", pollers);
-    for (int i = 0; i < 10; ++i) printf("%-14s %lld cycles\n", names[i], h[i]);
+    for (int i = 0; i < 12; ++i) printf("%-14s %lld cycles\n", names[i], h[i]);
     }
     return 0;
 }
