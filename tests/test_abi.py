@@ -45,7 +45,8 @@ def test_sass_is_blackwell_native():
     build.build_library()
     sass = subprocess.run([cuobjdump, "-sass", _lib.LIB_PATH], capture_output=True, text=True).stdout
     assert "sm_100a" in sass
-    for mnemonic in ("UTCHMMA", "LDTM", "UTMALDG", "UTMASTG", "UBLKCP"):
+    # STTM: the fine transformer writes its MMA A operands into tensor memory (tcgen05.st)
+    for mnemonic in ("UTCHMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP"):
         assert mnemonic in sass, mnemonic
 
 
@@ -83,3 +84,45 @@ def test_argument_errors(lib):
     assert lib.fm_coarse_workspace_bytes(1, 80, 80, 100, 0, 4) == 0
     assert lib.fm_coarse_workspace_bytes(32, 5120, 5120, 256, 0, 4) > 0
     assert lib.fm_fine_gather_workspace_bytes(32, 5120, 5120, 256, 64, 0) > 2 * 32 * 5120 * 64 * 4
+
+
+def test_fine_transformer_argument_errors(lib):
+    buf = (ctypes.c_char * 4096)()
+    p = ctypes.c_void_p((ctypes.addressof(buf) + 255) & ~255)
+    kinds = (ctypes.c_int32 * 2)(0, 1)
+    ptrs = (ctypes.c_void_p * 20)(*[p.value] * 20)
+    need = lib.fm_fine_transformer_workspace_bytes(2)
+    assert need >= 2 * 160 * 1024 and lib.fm_fine_transformer_workspace_bytes(0) == 0
+    call = lambda WW=49, C=64, nhead=8, ws=need, k=kinds, pp=ptrs, cap=4: lib.fm_fine_transformer(
+        p, p, None, cap, WW, C, nhead, 2, k, pp, p, p, p, ws, None)
+    assert call(WW=64) == -4 and b"WW" in lib.fm_last_error_string()      # FM_ERR_UNSUPPORTED
+    assert call(C=128) == -4 and call(nhead=4) == -4
+    assert call(ws=need - 1) == -2                                          # FM_ERR_WORKSPACE
+    assert call(k=(ctypes.c_int32 * 2)(0, 7)) == -1                         # bad layer kind
+    bad = (ctypes.c_void_p * 20)(*([p.value] * 19 + [None]))
+    assert call(pp=bad) == -1                                               # NULL parameter pointer
+    assert call(cap=0) == 0                                                 # nothing to do
+    if not torch.cuda.is_available():
+        assert call() == -3 and b"no CUDA device" in lib.fm_last_error_string()
+
+
+def test_transformer_module_keeps_reference_state_dict_keys():
+    """modules.LocalFeatureTransformer loads a reference fine-transformer state dict strictly
+    (network/module/transformer.py:59-76 parameter names) and refuses CPU tensors."""
+    from featurematching_b200 import modules
+    from oracle import reference_shims
+    cfg = reference_shims.default_config()["fine"]
+    m = modules.LocalFeatureTransformer(cfg)
+    keys = set(m.state_dict())
+    want = {f"layers.{i}.{n}" for i in range(2) for n in (
+        "q_proj.weight", "k_proj.weight", "v_proj.weight", "merge.weight", "mlp.0.weight", "mlp.2.weight",
+        "norm1.weight", "norm1.bias", "norm2.weight", "norm2.bias")}
+    assert keys == want
+    if reference_shims.available():
+        ref = reference_shims.load_reference().LocalFeatureTransformer(cfg)
+        m.load_state_dict(ref.state_dict(), strict=True)
+        assert set(ref.state_dict()) == keys
+    with pytest.raises(_lib.FmError):
+        m.eval()(torch.zeros(1, 49, 64), torch.zeros(1, 49, 64))
+    with pytest.raises(_lib.FmError):
+        modules.LocalFeatureTransformer(dict(cfg, attention="full"))

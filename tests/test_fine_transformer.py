@@ -141,6 +141,20 @@ def test_transformer_then_fine_match_within_1e3_px():
 
 
 @pytest.mark.gpu
+def test_transformer_zero_count_touches_nothing():
+    from featurematching_b200 import modules
+    m = modules.LocalFeatureTransformer({"d_model": 64, "nhead": 8, "layer_names": ["self", "cross"],
+                                         "attention": "linear"}).cuda().eval()
+    a = torch.full((6, 49, 64), 3.0, device="cuda"); b = torch.full((6, 49, 64), 4.0, device="cuda")
+    count = torch.zeros(1, dtype=torch.int32, device="cuda")
+    m.transform(a, b, count=count, out=(a, b))
+    torch.cuda.synchronize()
+    assert (a == 3.0).all() and (b == 4.0).all()
+    e0, e1 = m(torch.empty(0, 49, 64, device="cuda"), torch.empty(0, 49, 64, device="cuda"))
+    assert e0.shape == (0, 49, 64) and e1.shape == (0, 49, 64)
+
+
+@pytest.mark.gpu
 def test_transformer_rejects_unsupported():
     from featurematching_b200 import _lib, modules
     m = modules.LocalFeatureTransformer({"d_model": 64, "nhead": 8, "layer_names": ["self"],
