@@ -99,8 +99,9 @@ __global__ void __launch_bounds__(256) tf_pack_kernel(TfLayerParams p, uint8_t* 
 __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
     const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     hi = *reinterpret_cast<const uint32_t*>(&h);
-    const float ah = __uint_as_float(hi << 16), bh = __uint_as_float(hi & 0xffff0000u);
-    const __nv_bfloat162 l = __floats2bfloat162_rn(a - ah, b - bh);
+    float ra, rb;   // one packed subtraction for both residuals
+    unpack2(sub2(pack2(a, b), pack2(__uint_as_float(hi << 16), __uint_as_float(hi & 0xffff0000u))), ra, rb);
+    const __nv_bfloat162 l = __floats2bfloat162_rn(ra, rb);
     lo = *reinterpret_cast<const uint32_t*>(&l);
 }
 // 32 values of this thread's row -> A operand columns (hi at `thi`, lo at `tlo`, 16 columns each)
@@ -116,18 +117,21 @@ __device__ __forceinline__ float elu1(float x) { return x > 0.f ? x + 1.f : ex2_
 
 // mean and centred sum of squares of 32 values
 __device__ __forceinline__ float2 local_stats(const float (&v)[32]) {
-    float s0 = 0.f, s1 = 0.f;
+    uint64_t s = pack2(v[0], v[1]);   // packed fp32x2 arithmetic: one instruction per channel pair
 #pragma unroll
-    for (int i = 0; i < 32; i += 2) { s0 += v[i]; s1 += v[i + 1]; }
+    for (int i = 2; i < 32; i += 2) s = add2(s, pack2(v[i], v[i + 1]));
+    float s0, s1;
+    unpack2(s, s0, s1);
     const float mean = (s0 + s1) * (1.f / 32.f);
-    float m0 = 0.f, m1 = 0.f;
+    const uint64_t nm = pack2(-mean, -mean);
+    uint64_t m2 = pack2(0.f, 0.f);
 #pragma unroll
     for (int i = 0; i < 32; i += 2) {
-        const float d0 = v[i] - mean, d1 = v[i + 1] - mean;
-        m0 = fmaf(d0, d0, m0);
-        m1 = fmaf(d1, d1, m1);
+        const uint64_t d = add2(pack2(v[i], v[i + 1]), nm);
+        m2 = fma2(d, d, m2);
     }
-    return make_float2(mean, m0 + m1);
+    unpack2(m2, s0, s1);
+    return make_float2(mean, s0 + s1);
 }
 // LayerNorm over 64 channels from the two halves' statistics (Chan's combination), eps 1e-5
 __device__ __forceinline__ void layer_norm32(float (&v)[32], float2 mine, float2 other, const float* w, const float* b) {
@@ -135,14 +139,14 @@ __device__ __forceinline__ void layer_norm32(float (&v)[32], float2 mine, float2
     const float dm = mine.x - other.x;
     const float var = (mine.y + other.y + dm * dm * 16.f) * (1.f / 64.f);
     const float rstd = 1.0f / sqrtf(var + 1e-5f);
+    const uint64_t r2 = pack2(rstd, rstd), nm = pack2(-mean, -mean);
 #pragma unroll
-    for (int i = 0; i < 32; i += 4) {
+    for (int i = 0; i < 32; i += 4) {   // y = v * (rstd w) + (b - mean rstd w), two channels per instruction
         const float4 ww = *reinterpret_cast<const float4*>(w + i);
         const float4 bb = *reinterpret_cast<const float4*>(b + i);
-        v[i] = fmaf((v[i] - mean) * rstd, ww.x, bb.x);
-        v[i + 1] = fmaf((v[i + 1] - mean) * rstd, ww.y, bb.y);
-        v[i + 2] = fmaf((v[i + 2] - mean) * rstd, ww.z, bb.z);
-        v[i + 3] = fmaf((v[i + 3] - mean) * rstd, ww.w, bb.w);
+        const uint64_t a0 = mul2(pack2(ww.x, ww.y), r2), a1 = mul2(pack2(ww.z, ww.w), r2);
+        unpack2(fma2(pack2(v[i], v[i + 1]), a0, fma2(a0, nm, pack2(bb.x, bb.y))), v[i], v[i + 1]);
+        unpack2(fma2(pack2(v[i + 2], v[i + 3]), a1, fma2(a1, nm, pack2(bb.z, bb.w))), v[i + 2], v[i + 3]);
     }
 }
 
@@ -394,17 +398,22 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     const int w2 = st >> 7, d = (st & 127) >> 1, vh = st & 1;
                     const uint8_t* kp = scr + w2 * kMaxWW * kScrRow + d * 4;
                     const uint8_t* vp = scr + w2 * kMaxWW * kScrRow + 256 + (d >> 3) * 32 + vh * 16;
-                    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, ks = 0.f;
+                    uint64_t a01 = pack2(0.f, 0.f), a23 = a01;
+                    float ks = 0.f;
 #pragma unroll
                     for (int rr = 0; rr < kMaxWW; ++rr) {
                         if (kWW ? rr < kWW : rr < WW) {
                             const float kv = *reinterpret_cast<const float*>(kp + rr * kScrRow);
                             const float4 vv = *reinterpret_cast<const float4*>(vp + rr * kScrRow);
-                            a0 = fmaf(kv, vv.x, a0); a1 = fmaf(kv, vv.y, a1);
-                            a2 = fmaf(kv, vv.z, a2); a3 = fmaf(kv, vv.w, a3);
+                            const uint64_t k2 = pack2(kv, kv);
+                            a01 = fma2(k2, pack2(vv.x, vv.y), a01);
+                            a23 = fma2(k2, pack2(vv.z, vv.w), a23);
                             ks += kv;
                         }
                     }
+                    float a0, a1, a2, a3;
+                    unpack2(a01, a0, a1);
+                    unpack2(a23, a2, a3);
                     *reinterpret_cast<float4*>(kvm + (w2 * 64 + d) * 8 + vh * 4) = make_float4(a0, a1, a2, a3);
                     if (vh == 0) ksum[w2 * 64 + d] = ks;
                 }
@@ -429,24 +438,31 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     const int h = 4 * g + hh;
                     const float* kvp = kvm + (w * 64 + h * 8) * 8;
                     const float* ksp = ksum + w * 64 + h * 8;
-                    float den = 1e-6f, mm[8];
+                    float den = 1e-6f;
+                    uint64_t mm[4];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) mm[j] = 0.f;
+                    for (int j = 0; j < 4; ++j) mm[j] = pack2(0.f, 0.f);
 #pragma unroll
                     for (int dd = 0; dd < 8; ++dd) {
                         const float qd = qf[hh * 8 + dd];
                         const float4 ka = *reinterpret_cast<const float4*>(kvp + dd * 8);
                         const float4 kb = *reinterpret_cast<const float4*>(kvp + dd * 8 + 4);
+                        const uint64_t q2 = pack2(qd, qd);
                         den = fmaf(qd, ksp[dd], den);
-                        mm[0] = fmaf(qd, ka.x, mm[0]); mm[1] = fmaf(qd, ka.y, mm[1]);
-                        mm[2] = fmaf(qd, ka.z, mm[2]); mm[3] = fmaf(qd, ka.w, mm[3]);
-                        mm[4] = fmaf(qd, kb.x, mm[4]); mm[5] = fmaf(qd, kb.y, mm[5]);
-                        mm[6] = fmaf(qd, kb.z, mm[6]); mm[7] = fmaf(qd, kb.w, mm[7]);
+                        mm[0] = fma2(q2, pack2(ka.x, ka.y), mm[0]);
+                        mm[1] = fma2(q2, pack2(ka.z, ka.w), mm[1]);
+                        mm[2] = fma2(q2, pack2(kb.x, kb.y), mm[2]);
+                        mm[3] = fma2(q2, pack2(kb.z, kb.w), mm[3]);
                     }
                     const float z = 1.0f / den;
+                    const uint64_t z2 = pack2(z, z);
                     uint32_t hi[4], lo[4];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) split2(mm[2 * j] * z, mm[2 * j + 1] * z, hi[j], lo[j]);
+                    for (int j = 0; j < 4; ++j) {
+                        float ma, mb;
+                        unpack2(mul2(mm[j], z2), ma, mb);
+                        split2(ma, mb, hi[j], lo[j]);
+                    }
                     tmem_st_32x4(tl + 128 + 16 * g + 4 * hh, hi);
                     tmem_st_32x4(tl + 160 + 16 * g + 4 * hh, lo);
                 }
