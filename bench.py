@@ -415,7 +415,7 @@ def run_b200(args):
     ft_flops = M * 4 * 49 * 2.0 * (4 * 64 * 64 + 128 * 128 + 64 * 128)
     kernels["fine_transformer"] = {"bound": "tensor", "ms": ft_ms, "achieved": ft_flops / (ft_ms * 1e-3) / 1e12,
                                    "peak": pk["tflops_sustained"], "unit": "TFLOP/s",
-                                   "in_step": bool(args.with_fine_transformer),
+                                   "in_step": bool(args.with_fine_transformer), "traffic": load_traffic("fine_transformer"),
                                    "note": "fp32-equivalent flop; executed as 3-term bf16 splits, SIMT/latency-bound"}
     for kname, kv in kernels.items():
         kv["frac"] = kv["achieved"] / kv["peak"]
