@@ -161,6 +161,29 @@ def transformer_case(ref, name, M, layer_names, seed):
     print(f"{name}: M={M} layers={list(layer_names)} |out| max {o0.abs().max():.3f}")
 
 
+def fine_chain_with_transformer(ref, name):
+    """net.py:78-83 in full on the `fine_chain` inputs: the reference's FinePreprocess windows ->
+    its fine LocalFeatureTransformer (weights of the `fine_transformer` fixture) -> its FineMatching.
+    Stores only the final coordinates; inputs and weights live in the two fixtures it builds on."""
+    g = dict(np.load(os.path.join(GOLDEN_DIR, "fine_chain.npz")))
+    t = dict(np.load(os.path.join(GOLDEN_DIR, "fine_transformer.npz")))
+    cfg = reference_shims.default_config()
+    tr = ref.LocalFeatureTransformer(cfg["fine"]).eval()
+    tr.load_state_dict({k[3:]: torch.from_numpy(v) for k, v in t.items() if k.startswith("sd.")}, strict=True)
+    fin = ref.FineMatching(cfg["fine"]).eval()
+    with torch.no_grad():
+        fin.mix_feat_0.weight.copy_(torch.from_numpy(g["mix_w0"])[None]); fin.mix_feat_0.bias.copy_(torch.from_numpy(g["mix_b0"]))
+        fin.mix_feat_1.weight.copy_(torch.from_numpy(g["mix_w1"])[None]); fin.mix_feat_1.bias.copy_(torch.from_numpy(g["mix_b1"]))
+    data = {"hw0_i": tuple(g["hw_i"]), "hw0_f": tuple(g["hw_f"]),
+            "mkpts0_c": torch.from_numpy(g["mkpts0_c"]), "mkpts1_c": torch.from_numpy(g["mkpts1_c"])}
+    with torch.no_grad():
+        w0, w1 = tr(torch.from_numpy(g["win0"]), torch.from_numpy(g["win1"]))
+        fin(w0, w1, data)
+    np.savez_compressed(os.path.join(GOLDEN_DIR, name + ".npz"),
+                        mkpts0_f=data["mkpts0_f"].numpy(), mkpts1_f=data["mkpts1_f"].numpy())
+    print(f"{name}: mkpts0_f[0]={data['mkpts0_f'][0].tolist()}")
+
+
 def main():
     os.makedirs(GOLDEN_DIR, exist_ok=True)
     ref = reference_shims.load_reference()
@@ -176,6 +199,7 @@ def main():
     fine_match_special(ref, "fine_match_special", 31)
     transformer_case(ref, "fine_transformer", 12, ("self", "cross"), 41)
     transformer_case(ref, "fine_transformer_csc", 5, ("cross", "self", "cross"), 42)
+    fine_chain_with_transformer(ref, "fine_chain_tf")
 
 
 if __name__ == "__main__":

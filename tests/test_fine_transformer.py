@@ -194,3 +194,57 @@ def test_match_head_with_fine_transformer_vs_oracle():
     # without the transformer the coordinates differ: the stage is really in the chain
     ref_plain = mo.match_head(fc0, fc1, ff0, ff1, hw_i, hw_c, hw_c, hw_f, cfg["match_coarse"], p, p)
     assert (ref_plain["mkpts0_f"][:, :2] - ref["mkpts0_f"][:, :2]).abs().max() > 1e-2
+
+
+def _chain_inputs(golden_dir):
+    g = dict(np.load(os.path.join(golden_dir, "fine_chain.npz")))
+    _, sd, names = load(golden_dir, "fine_transformer")
+    want = dict(np.load(os.path.join(golden_dir, "fine_chain_tf.npz")))
+    return g, sd, names, want
+
+
+def test_chain_with_transformer_oracle_matches_reference_golden(golden_dir):
+    """FinePreprocess -> LocalFeatureTransformer -> FineMatching of the reference (net.py:78-83),
+    restated by the oracle from the raw feature maps."""
+    torch.set_num_threads(1)
+    g, sd, names, want = _chain_inputs(golden_dir)
+    t = {k: torch.from_numpy(v) for k, v in g.items() if v.dtype != np.uint16}
+    fc0, fc1 = compare.from_bits(g["feat_c0"]), compare.from_bits(g["feat_c1"])
+    ff0, ff1 = compare.from_bits(g["feat_f0"]), compare.from_bits(g["feat_f1"])
+    hw_c, hw_f, hw_i = tuple(g["hw_c"]), tuple(g["hw_f"]), tuple(g["hw_i"])
+    w0, w1 = mo.fine_preprocess(ff0, ff1, fc0, fc1, t["b_ids"], t["i_ids"], t["j_ids"], hw_c, hw_c, hw_f, 7, t)
+    layers = mo.transformer_params_from_state_dict(sd, len(names))
+    w0, w1 = mo.local_feature_transformer(w0, w1, layers, names, 8)
+    m0, m1 = mo.fine_match(w0, w1, t["mkpts0_c"], t["mkpts1_c"], t, hw_i, hw_f)
+    compare.check_fine(m0, m1, want["mkpts0_f"], want["mkpts1_f"])
+    assert (m0 - torch.from_numpy(want["mkpts0_f"])).abs().max() < 1e-4
+
+
+@pytest.mark.gpu
+def test_chain_with_transformer_kernels_match_reference_golden(golden_dir):
+    """The three CUDA stages chained (gather -> transformer -> fine match) against the reference's
+    own output for the same feature maps and weights: 1e-3 px (north_star)."""
+    from featurematching_b200 import modules
+    g, sd, names, want = _chain_inputs(golden_dir)
+    t = {k: torch.from_numpy(v) for k, v in g.items() if v.dtype != np.uint16}
+    dev = "cuda"
+    cfg = reference_shims.default_config()
+    pre = modules.FinePreprocess(cfg).eval().to(dev)
+    fin = modules.FineMatching(cfg["fine"]).eval().to(dev)
+    with torch.no_grad():
+        pre.down_proj.weight.copy_(t["down_w"]); pre.down_proj.bias.copy_(t["down_b"])
+        pre.merge_feat.weight.copy_(t["merge_w"]); pre.merge_feat.bias.copy_(t["merge_b"])
+        fin.mix_feat_0.weight.copy_(t["mix_w0"].reshape(1, -1)); fin.mix_feat_0.bias.copy_(t["mix_b0"].reshape(1))
+        fin.mix_feat_1.weight.copy_(t["mix_w1"].reshape(1, -1)); fin.mix_feat_1.bias.copy_(t["mix_b1"].reshape(1))
+    tr = _module(sd, names)
+    fc0, fc1 = compare.from_bits(g["feat_c0"]).to(dev), compare.from_bits(g["feat_c1"]).to(dev)
+    ff0, ff1 = compare.from_bits(g["feat_f0"]).to(dev), compare.from_bits(g["feat_f1"]).to(dev)
+    hw_c, hw_f, hw_i = tuple(g["hw_c"]), tuple(g["hw_f"]), tuple(g["hw_i"])
+    data = {"hw0_i": hw_i, "hw1_i": hw_i, "hw0_c": hw_c, "hw1_c": hw_c, "hw0_f": hw_f, "hw1_f": hw_f,
+            "b_ids": t["b_ids"].to(dev), "i_ids": t["i_ids"].to(dev), "j_ids": t["j_ids"].to(dev),
+            "mkpts0_c": t["mkpts0_c"].to(dev), "mkpts1_c": t["mkpts1_c"].to(dev)}
+    w0, w1 = pre(ff0, ff1, fc0, fc1, data)
+    w0, w1 = tr(w0, w1)
+    fin(w0, w1, data)
+    torch.cuda.synchronize()
+    compare.check_fine(data["mkpts0_f"], data["mkpts1_f"], want["mkpts0_f"], want["mkpts1_f"])
