@@ -43,6 +43,8 @@ SIGNATURES = {
     "fm_profile_collect": (_I, [_c.POINTER(_c.c_float), _c.POINTER(_c.c_int)]),
     "fm_fine_transformer_workspace_bytes": (_Z, [_I]),
     "fm_fine_transformer": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _Z, _P]),
+    "fm_coarse_transformer_workspace_bytes": (_Z, [_I, _I, _I, _I]),
+    "fm_coarse_transformer": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _Z, _P]),
     "fm_fine_match": (_I, [_P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _P, _P]),
 }
 

@@ -27,6 +27,7 @@
 
 #include "fm_common.cuh"
 #include "fm_ptx.cuh"
+#include "fm_tf_math.cuh"
 
 namespace fm {
 
@@ -95,15 +96,6 @@ __global__ void __launch_bounds__(256) tf_pack_kernel(TfLayerParams p, uint8_t* 
 }
 
 // ---------------------------------------------------------------- device helpers
-// (a, b) -> packed bf16 pair of the high parts and of the residuals a - ah, b - bh
-__device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
-    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-    hi = *reinterpret_cast<const uint32_t*>(&h);
-    float ra, rb;   // one packed subtraction for both residuals
-    unpack2(sub2(pack2(a, b), pack2(__uint_as_float(hi << 16), __uint_as_float(hi & 0xffff0000u))), ra, rb);
-    const __nv_bfloat162 l = __floats2bfloat162_rn(ra, rb);
-    lo = *reinterpret_cast<const uint32_t*>(&l);
-}
 // 32 values of this thread's row -> A operand columns (hi at `thi`, lo at `tlo`, 16 columns each)
 __device__ __forceinline__ void store_operand32(uint32_t thi, uint32_t tlo, const float (&v)[32]) {
     uint32_t hi[16], lo[16];
@@ -111,27 +103,6 @@ __device__ __forceinline__ void store_operand32(uint32_t thi, uint32_t tlo, cons
     for (int i = 0; i < 16; ++i) split2(v[2 * i], v[2 * i + 1], hi[i], lo[i]);
     tmem_st_32x16(thi, hi);
     tmem_st_32x16(tlo, lo);
-}
-// elu(x) + 1   (attentions.py:11-12)
-__device__ __forceinline__ float elu1(float x) { return x > 0.f ? x + 1.f : ex2_approx(x * 1.4426950408889634f); }
-
-// mean and centred sum of squares of 32 values
-__device__ __forceinline__ float2 local_stats(const float (&v)[32]) {
-    uint64_t s = pack2(v[0], v[1]);   // packed fp32x2 arithmetic: one instruction per channel pair
-#pragma unroll
-    for (int i = 2; i < 32; i += 2) s = add2(s, pack2(v[i], v[i + 1]));
-    float s0, s1;
-    unpack2(s, s0, s1);
-    const float mean = (s0 + s1) * (1.f / 32.f);
-    const uint64_t nm = pack2(-mean, -mean);
-    uint64_t m2 = pack2(0.f, 0.f);
-#pragma unroll
-    for (int i = 0; i < 32; i += 2) {
-        const uint64_t d = add2(pack2(v[i], v[i + 1]), nm);
-        m2 = fma2(d, d, m2);
-    }
-    unpack2(m2, s0, s1);
-    return make_float2(mean, s0 + s1);
 }
 // LayerNorm over 64 channels from the two halves' statistics (Chan's combination), eps 1e-5
 __device__ __forceinline__ void layer_norm32(float (&v)[32], float2 mine, float2 other, const float* w, const float* b) {

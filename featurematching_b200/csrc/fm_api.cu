@@ -173,6 +173,12 @@ cudaError_t launch_fine_match(const void* win0, const void* win1, int dtype, con
                               int capacity, int WW, float scale, float* out0, float* out1, int num_sms,
                               cudaStream_t st);
 
+bool coarse_transformer_supported(int C, int nhead);
+size_t coarse_transformer_workspace_bytes(int B, int L0, int L1, int n_layers);
+cudaError_t launch_coarse_transformer(const float* feat0, const float* feat1, int B, int L0, int L1, int n_layers,
+                                      const int* layer_kinds, const void* const* layer_params, float* out0,
+                                      float* out1, void* bf0, void* bf1, void* workspace, int num_sms,
+                                      cudaStream_t st);
 bool fine_transformer_supported(int C, int nhead, int WW);
 size_t fine_transformer_workspace_bytes(int n_layers);
 cudaError_t launch_fine_transformer(const float* win0, const float* win1, const int* count, int capacity, int WW,
@@ -468,6 +474,51 @@ int fm_fine_transformer(const float* win0, const float* win1, const int32_t* cou
     cudaError_t e = launch_fine_transformer(win0, win1, count, capacity, WW, n_layers, layer_kinds, layer_params, out0, out1,
                                             workspace, sms, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return cuda_fail(e, "fine_transformer launch");
+    return FM_OK;
+}
+
+size_t fm_coarse_transformer_workspace_bytes(int B, int L0, int L1, int n_layers) {
+    if (B < 0 || L0 < 0 || L1 < 0 || n_layers < 1) return 0;
+    return coarse_transformer_workspace_bytes(B, L0, L1, n_layers);
+}
+
+int fm_coarse_transformer(const float* feat0, const float* feat1, int B, int L0, int L1, int C, int nhead,
+                          int n_layers, const int32_t* layer_kinds, const float* const* layer_params, float* out0,
+                          float* out1, void* out0_bf16, void* out1_bf16, void* workspace, size_t workspace_bytes,
+                          void* stream) {
+    if (!layer_kinds || !layer_params || !workspace) { set_error("null pointer argument"); return FM_ERR_BAD_ARG; }
+    if (n_layers < 1 || n_layers > 32 || B < 0 || L0 < 0 || L1 < 0) { set_error("n_layers must be in [1, 32] and B, L0, L1 >= 0"); return FM_ERR_BAD_ARG; }
+    if ((static_cast<size_t>(B) * L0 && (!feat0 || !out0)) || (static_cast<size_t>(B) * L1 && (!feat1 || !out1))) {
+        set_error("null token pointer");
+        return FM_ERR_BAD_ARG;
+    }
+    if (!coarse_transformer_supported(C, nhead)) {
+        set_error("coarse transformer supports d_model 256, nhead 8 (got C=%d nhead=%d)", C, nhead);
+        return FM_ERR_UNSUPPORTED;
+    }
+    for (int l = 0; l < n_layers; ++l) {
+        if (layer_kinds[l] != 0 && layer_kinds[l] != 1) { set_error("layer_kinds[%d] must be 0 (self) or 1 (cross)", l); return FM_ERR_BAD_ARG; }
+        for (int k = 0; k < 10; ++k)
+            if (!layer_params[10 * l + k]) { set_error("layer_params[%d] is NULL", 10 * l + k); return FM_ERR_BAD_ARG; }
+    }
+    if ((reinterpret_cast<uintptr_t>(feat0) | reinterpret_cast<uintptr_t>(feat1) | reinterpret_cast<uintptr_t>(out0) |
+         reinterpret_cast<uintptr_t>(out1) | reinterpret_cast<uintptr_t>(out0_bf16) | reinterpret_cast<uintptr_t>(out1_bf16)) & 31) {
+        set_error("token pointers must be 32-byte aligned");
+        return FM_ERR_BAD_ARG;
+    }
+    if (reinterpret_cast<uintptr_t>(workspace) & 255) { set_error("workspace must be 256-byte aligned"); return FM_ERR_BAD_ARG; }
+    const size_t need = coarse_transformer_workspace_bytes(B, L0, L1, n_layers);
+    if (workspace_bytes < need) {
+        set_error("coarse transformer workspace too small: need %zu bytes, got %zu", need, workspace_bytes);
+        return FM_ERR_WORKSPACE;
+    }
+    if (B == 0 || (L0 == 0 && L1 == 0)) return FM_OK;
+    const int sms = sm_count();
+    if (sms <= 0) { set_error("no CUDA device available (this library has no CPU path)"); return FM_ERR_CUDA; }
+    cudaError_t e = launch_coarse_transformer(feat0, feat1, B, L0, L1, n_layers, layer_kinds,
+                                              reinterpret_cast<const void* const*>(layer_params), out0, out1, out0_bf16,
+                                              out1_bf16, workspace, sms, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "coarse_transformer launch");
     return FM_OK;
 }
 

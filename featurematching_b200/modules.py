@@ -371,8 +371,9 @@ class EncoderLayer(nn.Module):
 
 
 class LocalFeatureTransformer(nn.Module):
-    """network/module/transformer.py:59-97 for the FINE windows ([M, WW, 64], 8 heads, linear
-    attention) on the tcgen05 encoder-layer kernel.  Same constructor dict, parameter names
+    """network/module/transformer.py:59-97 on the tcgen05 kernels: the FINE windows ([M, WW, 64],
+    8 heads; fm_fine_transformer) or the COARSE tokens ([B, L, 256], 8 heads; fm_coarse_transformer),
+    chosen by config['d_model'].  Same constructor dict, parameter names
     (`layers.{i}.q_proj.weight` ...) and forward signature as the reference."""
 
     def __init__(self, config):
@@ -424,14 +425,51 @@ class LocalFeatureTransformer(nn.Module):
         self._keepalive = params   # the launch is asynchronous
         return o0, o1
 
+    def _packed_args(self, dev):
+        import ctypes
+        n = len(self.layers)
+        params = [t.detach().to(device=dev, dtype=torch.float32).contiguous()
+                  for layer in self.layers for t in layer.flat_parameters()]
+        kinds = (ctypes.c_int32 * n)(*[0 if k == 'self' else 1 for k in self.layer_names])
+        ptrs = (ctypes.c_void_p * (10 * n))(*[t.data_ptr() for t in params])
+        return n, params, kinds, ptrs
+
+    def transform_tokens(self, feat0, feat1, out=None, bf16_out=None):
+        """Coarse call (d_model 256): [B, L0, C], [B, L1, C] fp32 tokens -> updated tokens.  `bf16_out` =
+        optional pair of bf16 tensors of the same shapes that receive the rounded tokens (the
+        coarse matcher's inputs) in the same pass."""
+        lib = _lib.load()
+        _require_cuda(feat0, feat1)
+        f0 = feat0.to(torch.float32).contiguous()
+        f1 = feat1.to(torch.float32).contiguous()
+        B, L0, C = f0.shape
+        L1 = f1.shape[1]
+        if f1.shape[0] != B or f1.shape[2] != C:
+            raise _lib.FmError("feat0 / feat1 batch or channel mismatch")
+        dev = f0.device
+        o0, o1 = out if out is not None else (torch.empty_like(f0), torch.empty_like(f1))
+        b0, b1 = bf16_out if bf16_out is not None else (None, None)
+        n, params, kinds, ptrs = self._packed_args(dev)
+        nbytes = lib.fm_coarse_transformer_workspace_bytes(B, L0, L1, n)
+        ws = self._ws.get(max(nbytes, 256), dev)
+        with torch.cuda.device(dev):
+            rc = lib.fm_coarse_transformer(_lib.ptr(f0), _lib.ptr(f1), B, L0, L1, C, self.nhead, n, kinds, ptrs,
+                                           _lib.ptr(o0), _lib.ptr(o1), _lib.ptr(b0), _lib.ptr(b1),
+                                           _lib.ptr(ws), nbytes, _lib.stream_ptr(dev))
+        _lib.check(rc, "fm_coarse_transformer")
+        self._keepalive = params   # the launch is asynchronous
+        return o0, o1
+
     def forward(self, feat0, feat1, mask0=None, mask1=None):
-        """Same contract as transformer.py:78-97 (masks must be None, as at net.py:80)."""
+        """Same contract as transformer.py:78-97 (masks must be None, as at net.py:74,80)."""
         assert self.d_model == feat0.size(2), "the feature number of src and transformer must be equal"
         if mask0 is not None or mask1 is not None:
             raise NotImplementedError("LocalFeatureTransformer (B200): masks are not supported")
         if self.training:
             raise NotImplementedError("LocalFeatureTransformer (B200) is inference-only")
         with torch.no_grad():
+            if self.d_model == 256:
+                return self.transform_tokens(feat0, feat1)
             return self.transform(feat0, feat1)
 
 
@@ -460,5 +498,12 @@ def install(net):
         ft.load_state_dict(net.fine.state_dict(), strict=True)
         net._fm_reference['fine'] = net.fine
         net.fine = ft.to(dev)
+    coarse_cfg = cfg['coarse']
+    if (hasattr(net, 'coarse') and coarse_cfg.get('attention', 'linear') == 'linear'
+            and coarse_cfg['d_model'] == 256 and coarse_cfg['nhead'] == 8):
+        ct = LocalFeatureTransformer(coarse_cfg)
+        ct.load_state_dict(net.coarse.state_dict(), strict=True)
+        net._fm_reference['coarse'] = net.coarse
+        net.coarse = ct.to(dev)
     net.train(False)
     return net

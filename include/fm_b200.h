@@ -10,6 +10,7 @@
  *   fm_fine_match    <->  FineMatching.forward
  *                         network/utils/fine_matching_new.py:22-79      (called at network/net.py:83)
  *   fm_fine_transformer <-> LocalFeatureTransformer.forward on the fine windows
+ *   fm_coarse_transformer <-> LocalFeatureTransformer.forward on the coarse tokens
  *                         network/module/transformer.py:78-97           (called at network/net.py:80)
  *
  * Conventions
@@ -169,6 +170,23 @@ FM_API int fm_fine_transformer(const float* win0, const float* win1, const int32
                         int WW, int C, int nhead, int n_layers, const int32_t* layer_kinds,
                         const float* const* layer_params, float* out0, float* out1, void* workspace,
                         size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------- coarse stage: token transformer
+ * LocalFeatureTransformer on the 1/8-resolution tokens -- the producer of the coarse matcher's
+ * inputs (network/net.py:74 -> network/module/transformer.py:59-97; EncoderLayer transformer.py:34-57
+ * with LinearAttention attentions.py:22-46, no masks); semantics of 'self' / 'cross' as above.
+ * feat0 [B, L0, C], feat1 [B, L1, C] fp32; out0 / out1 the updated tokens (fp32; may alias feat).
+ * out0_bf16 / out1_bf16 (may be NULL): the same tokens rounded to bf16 -- exactly the tensors
+ * fm_coarse_match reads, written without a separate cast pass.  C must be 256, nhead 8 (the shipped
+ * coarse config, demo/net_config.py:20-25).  layer_kinds / layer_params as for fm_fine_transformer.
+ * workspace: fm_coarse_transformer_workspace_bytes(B, L0, L1, n_layers) bytes, 256-byte aligned;
+ * token pointers 32-byte aligned.  All GEMMs run on the tensor cores with fp32-grade 3-term bf16
+ * splits.  An empty side (L == 0) leaves the other side's tokens unchanged (copied to out). */
+FM_API size_t fm_coarse_transformer_workspace_bytes(int B, int L0, int L1, int n_layers);
+FM_API int fm_coarse_transformer(const float* feat0, const float* feat1, int B, int L0, int L1, int C,
+                          int nhead, int n_layers, const int32_t* layer_kinds,
+                          const float* const* layer_params, float* out0, float* out1, void* out0_bf16,
+                          void* out1_bf16, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------- match records
  * Packs the match list into 40-byte records for the cross-GPU gather (the analogue of the

@@ -17,7 +17,7 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 from featurematching_b200 import synth  # noqa: E402
-from oracle import reference_shims  # noqa: E402
+from oracle import matcher_oracle as mo, reference_shims  # noqa: E402
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
                           "tests", "golden")
@@ -161,6 +161,27 @@ def transformer_case(ref, name, M, layer_names, seed):
     print(f"{name}: M={M} layers={list(layer_names)} |out| max {o0.abs().max():.3f}")
 
 
+COARSE_TF_CASE = dict(seed=4242, B=2, L0=200, L1=136, layer_names=["self", "cross"] * 4)
+
+
+def coarse_transformer_case(ref, name):
+    """The reference's COARSE LocalFeatureTransformer (net.py:74; d_model 256, 8 heads, the shipped
+    ['self', 'cross'] * 4) on seeded tokens with seeded parameters (oracle.matcher_oracle.seeded_*):
+    21 MB of parameters are not committed, only the reference's outputs for them."""
+    c = COARSE_TF_CASE
+    cfg = dict(reference_shims.default_config()["coarse"], layer_names=list(c["layer_names"]))
+    t = ref.LocalFeatureTransformer(cfg).eval()
+    layers = mo.seeded_transformer_layers(c["seed"], cfg["d_model"], len(c["layer_names"]))
+    t.load_state_dict(mo.state_dict_from_transformer_layers(layers), strict=True)
+    f0, f1 = mo.seeded_tokens(c["seed"] + 1, c["B"], c["L0"], c["L1"], cfg["d_model"])
+    with torch.no_grad():
+        o0, o1 = t(f0, f1)
+    np.savez_compressed(os.path.join(GOLDEN_DIR, name + ".npz"), out0=o0.numpy(), out1=o1.numpy(),
+                        seed=c["seed"], B=c["B"], L0=c["L0"], L1=c["L1"],
+                        layer_names=np.array(c["layer_names"]), nhead=cfg["nhead"], d_model=cfg["d_model"])
+    print(f"{name}: |out| max {o0.abs().max():.3f} mean {o0.abs().mean():.3f}")
+
+
 def fine_chain_with_transformer(ref, name):
     """net.py:78-83 in full on the `fine_chain` inputs: the reference's FinePreprocess windows ->
     its fine LocalFeatureTransformer (weights of the `fine_transformer` fixture) -> its FineMatching.
@@ -200,6 +221,7 @@ def main():
     transformer_case(ref, "fine_transformer", 12, ("self", "cross"), 41)
     transformer_case(ref, "fine_transformer_csc", 5, ("cross", "self", "cross"), 42)
     fine_chain_with_transformer(ref, "fine_chain_tf")
+    coarse_transformer_case(ref, "coarse_transformer")
 
 
 if __name__ == "__main__":

@@ -274,3 +274,48 @@ def transformer_params_from_state_dict(sd, n_layers, prefix=""):
                     "norm1_w": sd[k + "norm1.weight"], "norm1_b": sd[k + "norm1.bias"],
                     "norm2_w": sd[k + "norm2.weight"], "norm2_b": sd[k + "norm2.bias"]})
     return out
+
+
+# --------------------------------------------------------------------------- seeded fixtures
+def seeded_transformer_layers(seed, d_model, n_layers):
+    """Deterministic per-layer parameter dicts (numpy RandomState, so the values do not depend on the
+    torch version): Xavier-uniform matrices as transformer.py:73-76 draws them, LayerNorm affine
+    parameters away from (1, 0) so they matter.  Too large to commit for d_model 256 -- the coarse
+    golden fixture stores the seed and the reference's OUTPUTS for these parameters."""
+    import numpy as np
+    rs = np.random.RandomState(seed)
+    C = d_model
+
+    def xavier(n_out, n_in):
+        bound = math.sqrt(6.0 / (n_in + n_out))
+        return torch.from_numpy(rs.uniform(-bound, bound, size=(n_out, n_in)).astype(np.float32))
+
+    def uni(lo, hi):
+        return torch.from_numpy(rs.uniform(lo, hi, size=(C,)).astype(np.float32))
+
+    layers = []
+    for _ in range(n_layers):
+        layers.append({"q": xavier(C, C), "k": xavier(C, C), "v": xavier(C, C), "merge": xavier(C, C),
+                       "mlp0": xavier(2 * C, 2 * C), "mlp2": xavier(C, 2 * C),
+                       "norm1_w": uni(0.5, 1.5), "norm1_b": uni(-0.3, 0.3),
+                       "norm2_w": uni(0.5, 1.5), "norm2_b": uni(-0.3, 0.3)})
+    return layers
+
+
+def state_dict_from_transformer_layers(layers):
+    """Inverse of transformer_params_from_state_dict."""
+    names = {"q": "q_proj.weight", "k": "k_proj.weight", "v": "v_proj.weight", "merge": "merge.weight",
+             "mlp0": "mlp.0.weight", "mlp2": "mlp.2.weight", "norm1_w": "norm1.weight", "norm1_b": "norm1.bias",
+             "norm2_w": "norm2.weight", "norm2_b": "norm2.bias"}
+    return {f"layers.{i}.{names[k]}": v for i, p in enumerate(layers) for k, v in p.items()}
+
+
+def seeded_tokens(seed, B, L0, L1, C):
+    """Deterministic coarse token sequences (bf16-representable fp32), image 1 correlated with image 0."""
+    import numpy as np
+    rs = np.random.RandomState(seed)
+    f0 = torch.from_numpy(rs.standard_normal((B, L0, C)).astype(np.float32))
+    f1 = torch.from_numpy(rs.standard_normal((B, L1, C)).astype(np.float32))
+    n = min(L0, L1)
+    f1[:, :n] = 0.7 * f0[:, :n] + 0.3 * f1[:, :n]
+    return f0.to(torch.bfloat16).float(), f1.to(torch.bfloat16).float()
