@@ -123,8 +123,9 @@ __global__ void __launch_bounds__(256) ct_split_kernel(const float4* __restrict_
 
 // ---------------------------------------------------------------- K'^T V (attentions.py:42-43)
 // grid (chunks, B); one warp per head; a lane owns a 4 (d) x 8 (v) patch of the head's 32 x 32
-// matrix.  Tokens stream through shared memory 16 at a time.  Partial sums per (image, chunk) are
-// written, not accumulated atomically, so the result does not depend on scheduling.
+// matrix.  Tokens stream through shared memory 16 at a time, the next 16 already in flight in
+// registers; the products are packed f32x2 FMAs.  Partial sums per (image, chunk) are written, not
+// accumulated atomically, so the result does not depend on scheduling.
 __global__ void __launch_bounds__(256) ct_kv_partial_kernel(const float* __restrict__ kf, const float* __restrict__ vf,
                                                             int L, float* __restrict__ kvpart,
                                                             float* __restrict__ kspart) {
@@ -134,64 +135,89 @@ __global__ void __launch_bounds__(256) ct_kv_partial_kernel(const float* __restr
     const int h = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int dg = lane >> 2, vg = lane & 3;
     const int t0 = chunk * kKvChunk, t1 = min(t0 + kKvChunk, L);
-    float acc[4][8];
-    float ks[4] = {0.f, 0.f, 0.f, 0.f};
+    uint64_t acc[4][4];   // [d][v pair]
+    uint64_t ks[2] = {0ull, 0ull};
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0ull;
+    float4 pk[4], pv[4];
+    auto fetch = [&](int t) {
+        const int n4 = min(16, t1 - t) * (kD / 4);
+        const float4* gk = reinterpret_cast<const float4*>(kf + (static_cast<size_t>(b) * L + t) * kD);
+        const float4* gv = reinterpret_cast<const float4*>(vf + (static_cast<size_t>(b) * L + t) * kD);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int e = threadIdx.x + i * 256;
+            if (e < n4) { pk[i] = __ldg(gk + e); pv[i] = __ldg(gv + e); }
+        }
+    };
+    if (t0 < t1) fetch(t0);
     for (int t = t0; t < t1; t += 16) {
         const int nt = min(16, t1 - t);
         __syncthreads();
-        const float4* gk = reinterpret_cast<const float4*>(kf + (static_cast<size_t>(b) * L + t) * kD);
-        const float4* gv = reinterpret_cast<const float4*>(vf + (static_cast<size_t>(b) * L + t) * kD);
-        for (int e = threadIdx.x; e < nt * (kD / 4); e += 256) {
-            reinterpret_cast<float4*>(&sk[0][0])[e] = gk[e];
-            reinterpret_cast<float4*>(&sv[0][0])[e] = gv[e];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int e = threadIdx.x + i * 256;
+            if (e < nt * (kD / 4)) {
+                reinterpret_cast<float4*>(&sk[0][0])[e] = pk[i];
+                reinterpret_cast<float4*>(&sv[0][0])[e] = pv[i];
+            }
         }
         __syncthreads();
+        if (t + 16 < t1) fetch(t + 16);
         for (int r = 0; r < nt; ++r) {
             const float4 k4 = *reinterpret_cast<const float4*>(&sk[r][h * kHd + dg * 4]);
-            const float4 va = *reinterpret_cast<const float4*>(&sv[r][h * kHd + vg * 8]);
-            const float4 vb = *reinterpret_cast<const float4*>(&sv[r][h * kHd + vg * 8 + 4]);
+            const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(&sv[r][h * kHd + vg * 8]);
+            const ulonglong2 vb = *reinterpret_cast<const ulonglong2*>(&sv[r][h * kHd + vg * 8 + 4]);
+            ks[0] = add2(ks[0], pack2(k4.x, k4.y));
+            ks[1] = add2(ks[1], pack2(k4.z, k4.w));
             const float kk[4] = {k4.x, k4.y, k4.z, k4.w};
-            const float vv[8] = {va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w};
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                ks[i] += kk[i];
-#pragma unroll
-                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(kk[i], vv[j], acc[i][j]);
+                const uint64_t k2 = pack2(kk[i], kk[i]);
+                acc[i][0] = fma2(k2, va.x, acc[i][0]);
+                acc[i][1] = fma2(k2, va.y, acc[i][1]);
+                acc[i][2] = fma2(k2, vb.x, acc[i][2]);
+                acc[i][3] = fma2(k2, vb.y, acc[i][3]);
             }
         }
     }
     float* out = kvpart + ((static_cast<size_t>(b) * nchunks + chunk) * kH + h) * (kHd * kHd);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        float* row = out + (dg * 4 + i) * kHd + vg * 8;
-        *reinterpret_cast<float4*>(row) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
-        *reinterpret_cast<float4*>(row + 4) = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+        ulonglong2* row = reinterpret_cast<ulonglong2*>(out + (dg * 4 + i) * kHd + vg * 8);
+        row[0] = make_ulonglong2(acc[i][0], acc[i][1]);
+        row[1] = make_ulonglong2(acc[i][2], acc[i][3]);
     }
     if (vg == 0)
-        *reinterpret_cast<float4*>(kspart + (static_cast<size_t>(b) * nchunks + chunk) * kD + h * kHd + dg * 4) =
-            make_float4(ks[0], ks[1], ks[2], ks[3]);
+        *reinterpret_cast<ulonglong2*>(kspart + (static_cast<size_t>(b) * nchunks + chunk) * kD + h * kHd + dg * 4) =
+            make_ulonglong2(ks[0], ks[1]);
 }
 
-// grid (B): chunk partials summed in chunk order; KV[h][d][v] -> planes of the block-diagonal B operand
-// kvbd[b][plane][n = h*32 + v][k = h*32 + d] (off-diagonal blocks are zeroed once per call), sum K' -> ksum
+// grid (heads, B): chunk partials summed in chunk order; KV[h][d][v] -> planes of the block-diagonal B
+// operand kvbd[b][plane][n = h*32 + v][k = h*32 + d] (off-diagonal blocks are zeroed once per call),
+// sum K' -> ksum.  A thread owns four consecutive v of one d (coalesced float4 partial reads).
 __global__ void __launch_bounds__(256) ct_kv_finalize_kernel(const float* __restrict__ kvpart,
                                                              const float* __restrict__ kspart, int nchunks,
                                                              __nv_bfloat16* __restrict__ kvbd, float* __restrict__ ksum) {
-    const int b = blockIdx.x;
-    for (int e = threadIdx.x; e < kH * kHd * kHd; e += 256) {
-        const int h = e >> 10, d = (e >> 5) & 31, v = e & 31;
-        float s = 0.f;
-        for (int c = 0; c < nchunks; ++c) s += kvpart[(static_cast<size_t>(b) * nchunks + c) * (kH * kHd * kHd) + e];
-        put_planes(kvbd + static_cast<size_t>(b) * 2 * kD * kD, kD * kD, static_cast<size_t>(h * kHd + v) * kD + h * kHd + d, s);
+    const int h = blockIdx.x, b = blockIdx.y;
+    const int d = threadIdx.x >> 3, v0 = (threadIdx.x & 7) * 4;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int c = 0; c < nchunks; ++c) {
+        const float4 t = *reinterpret_cast<const float4*>(
+            kvpart + ((static_cast<size_t>(b) * nchunks + c) * kH + h) * (kHd * kHd) + threadIdx.x * 4);
+        s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
     }
-    {
-        float s = 0.f;
-        for (int c = 0; c < nchunks; ++c) s += kspart[(static_cast<size_t>(b) * nchunks + c) * kD + threadIdx.x];
-        ksum[static_cast<size_t>(b) * kD + threadIdx.x] = s;
+    __nv_bfloat16* dst = kvbd + static_cast<size_t>(b) * 2 * kD * kD;
+    const float sv[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        put_planes(dst, kD * kD, static_cast<size_t>(h * kHd + v0 + i) * kD + h * kHd + d, sv[i]);
+    if (threadIdx.x < kHd) {
+        float t = 0.f;
+        for (int c = 0; c < nchunks; ++c) t += kspart[(static_cast<size_t>(b) * nchunks + c) * kD + h * kHd + threadIdx.x];
+        ksum[static_cast<size_t>(b) * kD + h * kHd + threadIdx.x] = t;
     }
 }
 
@@ -338,16 +364,22 @@ ct_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
             const bool valid = row < p.L;
             const size_t gr = static_cast<size_t>(b) * p.L + row;
             const uint32_t buf = tile_it & 1, tph = (tile_it >> 1) & 1;
+            if (kEpi == kEpiLNRes && valid) {   // the residual row: in L2 by the time the second pass wants it
+                const float* xr = p.x + gr * kD + g * 128;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(xr + i * 32));
+            }
             mbar_wait(&ctl->t_full[buf], tph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * kTN + g * 128;
-            float v[32];
+            uint32_t ra[32], rb[32];   // two chunks of the accumulator row: chunk c+1 loads while chunk c is processed
 
-            if (kEpi == kEpiKV) {
-                float* dst = (nt == 0 ? p.f32_a : p.f32_b) + gr * kD + g * 128;
-#pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
-                    load_chunk(taddr + c * 32, v);
+            // ---- one 32-column chunk, everything but LayerNorm
+            auto chunk = [&](int c, const uint32_t (&r)[32]) {
+                float v[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+                if (kEpi == kEpiKV) {
                     if (nt == 0) {
 #pragma unroll
                         for (int i = 0; i < 32; ++i) v[i] = elu1(v[i]);
@@ -356,90 +388,107 @@ ct_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
                         for (int i = 0; i < 32; ++i) v[i] *= p.inv_len;
                     }
                     if (valid) {
+                        float* dst = (nt == 0 ? p.f32_a : p.f32_b) + gr * kD + g * 128 + c * 32;
 #pragma unroll
-                        for (int i = 0; i < 32; i += 8) stg256(dst + c * 32, v, i);
+                        for (int i = 0; i < 32; i += 8) stg256(dst, v, i);
                     }
-                }
-            } else if (kEpi == kEpiQ || kEpi == kEpiMsg) {
-#pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
+                } else if (kEpi == kEpiQ) {
                     const int h = g * 4 + c;   // a 32-column chunk is one head
-                    load_chunk(taddr + c * 32, v);
-                    if (kEpi == kEpiQ) {
-                        const float4* ks = reinterpret_cast<const float4*>(p.ksum + static_cast<size_t>(b) * kD + h * kHd);
-                        float den = 0.f;
+                    const float4* ks = reinterpret_cast<const float4*>(p.ksum + static_cast<size_t>(b) * kD + h * kHd);
+                    float den = 0.f;
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const float4 k4 = __ldg(ks + i);
-                            v[4 * i] = elu1(v[4 * i]); v[4 * i + 1] = elu1(v[4 * i + 1]);
-                            v[4 * i + 2] = elu1(v[4 * i + 2]); v[4 * i + 3] = elu1(v[4 * i + 3]);
-                            den = fmaf(v[4 * i], k4.x, den); den = fmaf(v[4 * i + 1], k4.y, den);
-                            den = fmaf(v[4 * i + 2], k4.z, den); den = fmaf(v[4 * i + 3], k4.w, den);
-                        }
-                        if (valid) p.z[gr * kH + h] = 1.0f / (den + 1e-6f);
-                    } else {
-                        const float zz = valid ? p.z[gr * kH + h] : 0.f;
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) v[i] = v[i] * zz * p.len;
+                    for (int i = 0; i < 8; ++i) {
+                        const float4 k4 = __ldg(ks + i);
+                        v[4 * i] = elu1(v[4 * i]); v[4 * i + 1] = elu1(v[4 * i + 1]);
+                        v[4 * i + 2] = elu1(v[4 * i + 2]); v[4 * i + 3] = elu1(v[4 * i + 3]);
+                        den = fmaf(v[4 * i], k4.x, den); den = fmaf(v[4 * i + 1], k4.y, den);
+                        den = fmaf(v[4 * i + 2], k4.z, den); den = fmaf(v[4 * i + 3], k4.w, den);
                     }
+                    if (valid) {
+                        p.z[gr * kH + h] = 1.0f / (den + 1e-6f);
+                        store_planes32(p.planes + gr * p.ld + h * kHd, p.plane_stride, v);
+                    }
+                } else if (kEpi == kEpiMsg) {
+                    const int h = g * 4 + c;
+                    const float zz = valid ? p.z[gr * kH + h] : 0.f;
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] = v[i] * zz * p.len;
                     if (valid) store_planes32(p.planes + gr * p.ld + h * kHd, p.plane_stride, v);
-                }
-            } else if (kEpi == kEpiRelu) {
-#pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
-                    load_chunk(taddr + c * 32, v);
+                } else if (kEpi == kEpiRelu) {
 #pragma unroll
                     for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
                     if (valid) store_planes32(p.planes + gr * p.ld + nt * kTN + g * 128 + c * 32, p.plane_stride, v);
                 }
-            } else {
-                // LayerNorm over the row's 256 columns: this thread's 128 (Chan's combination of its four
-                // 32-column chunks), then the other half's statistics through shared memory
-                float mean = 0.f, m2 = 0.f;
-#pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
-                    load_chunk(taddr + c * 32, v);
-                    const float2 st = local_stats(v);
-                    const float na = 32.f * c, n = na + 32.f, dlt = st.x - mean;
-                    mean += dlt * (32.f / n);
-                    m2 += st.y + dlt * dlt * (na * 32.f / n);
+            };
+            // ---- LayerNorm, pass 1: Chan's combination of the chunk statistics
+            float mean = 0.f, m2 = 0.f, mu = 0.f, rstd = 0.f;
+            auto stats = [&](int c, const uint32_t (&r)[32]) {
+                float v[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+                const float2 st = local_stats(v);
+                const float na = 32.f * c, n = na + 32.f, dlt = st.x - mean;
+                mean += dlt * (32.f / n);
+                m2 += st.y + dlt * dlt * (na * 32.f / n);
+            };
+            // ---- LayerNorm, pass 2: normalise, (residual,) store
+            auto norm = [&](int c, const uint32_t (&r)[32]) {
+                const int col = g * 128 + c * 32;
+                float v[32];
+                const uint64_t r2 = pack2(rstd, rstd), nm = pack2(-mu, -mu);
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {   // y = v * (rstd w) + (b - mu rstd w), two channels per instruction
+                    const float4 ww = *reinterpret_cast<const float4*>(&ctl->lnp[col + i]);
+                    const float4 bb = *reinterpret_cast<const float4*>(&ctl->lnp[kD + col + i]);
+                    const uint64_t a0 = mul2(pack2(ww.x, ww.y), r2), a1 = mul2(pack2(ww.z, ww.w), r2);
+                    unpack2(fma2(pack2(__uint_as_float(r[i]), __uint_as_float(r[i + 1])), a0, fma2(a0, nm, pack2(bb.x, bb.y))),
+                            v[i], v[i + 1]);
+                    unpack2(fma2(pack2(__uint_as_float(r[i + 2]), __uint_as_float(r[i + 3])), a1, fma2(a1, nm, pack2(bb.z, bb.w))),
+                            v[i + 2], v[i + 3]);
                 }
+                if (valid) {
+                    if (kEpi == kEpiLNRes) {
+                        float xv[32];   // prefetched into L2 at the top of the tile
+#pragma unroll
+                        for (int i = 0; i < 32; i += 8) ldg256(p.x + gr * kD + col, xv, i);
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) v[i] += xv[i];
+#pragma unroll
+                        for (int i = 0; i < 32; i += 8) stg256(p.x + gr * kD + col, v, i);
+                    }
+                    store_planes32(p.planes + gr * p.ld + col, p.plane_stride, v);
+                }
+            };
+            // chunk c+1 is in flight while chunk c is processed
+#define CT_PIPE4(F)                                                        \
+    tmem_ld_32x32(taddr, ra);                                              \
+    tmem_ld_wait_dep(ra); tmem_ld_32x32(taddr + 32, rb); F(0, ra);         \
+    tmem_ld_wait_dep(rb); tmem_ld_32x32(taddr + 64, ra); F(1, rb);         \
+    tmem_ld_wait_dep(ra); tmem_ld_32x32(taddr + 96, rb); F(2, ra);         \
+    tmem_ld_wait_dep(rb); F(3, rb);
+
+#ifdef CT_EPI_NOP   // mainloop-only timing (tools/dbg_build.sh)
+            if (p.L >= 0) {
+            } else
+#endif
+            if (!kNorm) {
+                CT_PIPE4(chunk)
+            } else {
+                CT_PIPE4(stats)
                 const uint32_t lb = tile_it & 1;
                 ctl->lnx[lb][rl][g] = make_float2(mean, m2);
+                tmem_ld_32x32(taddr, ra);   // pass 2's first chunk loads across the barrier
                 named_bar_sync(1, kEpiThreads);
                 const float2 other = ctl->lnx[lb][rl][g ^ 1];
                 const float dm = mean - other.x;
-                const float mu = 0.5f * (mean + other.x);
-                const float var = (m2 + other.y + dm * dm * 64.f) * (1.f / 256.f);
-                const float rstd = 1.0f / sqrtf(var + 1e-5f);
-#pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
-                    const int col = g * 128 + c * 32;
-                    load_chunk(taddr + c * 32, v);
-#pragma unroll
-                    for (int i = 0; i < 32; i += 4) {
-                        const float4 ww = *reinterpret_cast<const float4*>(&ctl->lnp[col + i]);
-                        const float4 bb = *reinterpret_cast<const float4*>(&ctl->lnp[kD + col + i]);
-                        v[i] = fmaf((v[i] - mu) * rstd, ww.x, bb.x);
-                        v[i + 1] = fmaf((v[i + 1] - mu) * rstd, ww.y, bb.y);
-                        v[i + 2] = fmaf((v[i + 2] - mu) * rstd, ww.z, bb.z);
-                        v[i + 3] = fmaf((v[i + 3] - mu) * rstd, ww.w, bb.w);
-                    }
-                    if (valid) {
-                        if (kEpi == kEpiLNRes) {
-                            float* xr = p.x + gr * kD + col;
-                            float xv[32];
-#pragma unroll
-                            for (int i = 0; i < 32; i += 8) ldg256(xr, xv, i);
-#pragma unroll
-                            for (int i = 0; i < 32; ++i) v[i] += xv[i];
-#pragma unroll
-                            for (int i = 0; i < 32; i += 8) stg256(xr, v, i);
-                        }
-                        store_planes32(p.planes + gr * p.ld + col, p.plane_stride, v);
-                    }
-                }
+                mu = 0.5f * (mean + other.x);
+                rstd = 1.0f / sqrtf((m2 + other.y + dm * dm * 64.f) * (1.f / 256.f) + 1e-5f);
+                tmem_ld_wait_dep(ra); tmem_ld_32x32(taddr + 32, rb); norm(0, ra);
+                tmem_ld_wait_dep(rb); tmem_ld_32x32(taddr + 64, ra); norm(1, rb);
+                tmem_ld_wait_dep(ra); tmem_ld_32x32(taddr + 96, rb); norm(2, ra);
+                tmem_ld_wait_dep(rb); norm(3, rb);
             }
+#undef CT_PIPE4
             // release the accumulator buffer to the MMA warp
             tc_fence_before();
             __syncwarp();
@@ -616,7 +665,7 @@ cudaError_t launch_coarse_transformer(const float* feat0, const float* feat1, in
             // 2. K'^T V
             const int chunks = (S + kKvChunk - 1) / kKvChunk;
             ct_kv_partial_kernel<<<dim3(chunks, B), 256, 0, st>>>(kf, vf, S, kvpart, kspart);
-            ct_kv_finalize_kernel<<<B, 256, 0, st>>>(kvpart, kspart, chunks, kvbd, ksum);
+            ct_kv_finalize_kernel<<<dim3(kH, B), 256, 0, st>>>(kvpart, kspart, chunks, kvbd, ksum);
             // 3. Q', Z
             p.L = Lx; p.planes = qp; p.plane_stride = Rx * kD; p.ld = kD; p.ksum = ksum; p.z = z;
             if ((e = launch_gemm<kEpiQ>(m_x[xs_], m_x[xs_], w_q, p, kD, kD, num_sms, st)) != cudaSuccess) return e;
