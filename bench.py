@@ -8,6 +8,8 @@ fine dual-correlate match -> match-record pack [+ cross-GPU gather when N > 1]) 
 synthetic frame pairs: BASELINE.json configs[1], 32 planted 640x512-shaped pairs per GPU, bf16
 features.  The fine transformer is timed beside the step and reported
 under kernels.fine_transformer; --with-fine-transformer puts it inside the step on both arms.
+The coarse transformer (8(f) rank 2, the producer of the coarse tokens) is timed beside the step
+on the step's tokens and reported under kernels.coarse_transformer.
 Prints ONE JSON line (rank 0).  `--impl reference` times the CPU restatement of the reference
 (oracle/, the reference itself cannot travel to the GPU box) on the host cores instead.
 """
@@ -57,6 +59,8 @@ def parse_args():
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-coarse-transformer", action="store_true",
+                    help="skip the coarse LocalFeatureTransformer stage (timed beside the step, kernels.coarse_transformer)")
     ap.add_argument("--with-fine-transformer", action="store_true",
                     help="put the fine LocalFeatureTransformer (SURVEY.md 8(f) rank 1, net.py:79-80) INSIDE the step, "
                          "between gather and fine match (GPU and CPU arms alike); by default it is timed beside "
@@ -151,6 +155,17 @@ def fine_transformer_module():
     from featurematching_b200 import modules
     torch.manual_seed(77)
     return modules.LocalFeatureTransformer(FINE_CFG).eval()
+
+
+COARSE_CFG = {"d_model": 256, "nhead": 8, "layer_names": ["self", "cross"] * 4, "attention": "linear"}   # demo/net_config.py:20-25
+
+
+def coarse_transformer_module():
+    """The coarse LocalFeatureTransformer with seeded random-init weights."""
+    import torch
+    from featurematching_b200 import modules
+    torch.manual_seed(78)
+    return modules.LocalFeatureTransformer(COARSE_CFG).eval()
 
 
 def cpu_head_factory(args):
@@ -363,6 +378,23 @@ def run_b200(args):
         torch.cuda.synchronize()
         ft_ms = fe[0].elapsed_time(fe[1]) / 5
         del o
+    # coarse transformer (the producer of fc0 / fc1 in the full network): timed beside the step on fp32
+    # copies of the step's tokens -- with random-init weights it would scramble the planted matches
+    ct_ms = None
+    if not args.no_coarse_transformer:
+        ctm = coarse_transformer_module().to(dev)
+        t0f, t1f = fc0.float().contiguous(), fc1.float().contiguous()
+        o = (torch.empty_like(t0f), torch.empty_like(t1f))
+        for _ in range(2):
+            ctm.transform_tokens(t0f, t1f, out=o)
+        fe = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        fe[0].record()
+        for _ in range(3):
+            ctm.transform_tokens(t0f, t1f, out=o)
+        fe[1].record()
+        torch.cuda.synchronize()
+        ct_ms = fe[0].elapsed_time(fe[1]) / 3
+        del o, t0f, t1f, ctm
     ms_step = ms_total / K
     value = world * B * K / (ms_total * 1e-3)
 
@@ -417,6 +449,14 @@ def run_b200(args):
                                    "peak": pk["tflops_sustained"], "unit": "TFLOP/s",
                                    "in_step": bool(args.with_fine_transformer), "traffic": load_traffic("fine_transformer"),
                                    "note": "fp32-equivalent flop; executed as 3-term bf16 splits, SIMT/latency-bound"}
+    if ct_ms is not None:
+        # 8 encoder layers x 2 sides x B x N rows x (q, k, v, merge 4 x 256^2 + mlp 512^2 + 256 x 512) MACs
+        ct_flops = len(COARSE_CFG["layer_names"]) * 2 * B * N * 2.0 * (4 * 256 * 256 + 512 * 512 + 256 * 512)
+        kernels["coarse_transformer"] = {"bound": "tensor", "ms": ct_ms, "achieved": ct_flops / (ct_ms * 1e-3) / 1e12,
+                                         "peak": pk["tflops_sustained"], "unit": "TFLOP/s", "in_step": False,
+                                         "traffic": load_traffic("coarse_transformer"),
+                                         "note": "fp32-equivalent flop of the reference's GEMMs; executed as 3-term bf16 "
+                                                 "splits (3x the tensor work) plus the blockdiag(KV) product"}
     for kname, kv in kernels.items():
         kv["frac"] = kv["achieved"] / kv["peak"]
         kv["share_of_step"] = kv["ms"] / ms_step
@@ -439,8 +479,8 @@ def run_b200(args):
                    "l2": f"inputs ({in_bytes / 1e6:.0f} MB/step) exceed the 126 MB L2; no explicit flush",
                    "windows": "fp32 (what the reference hands to its fine transformer)"},
         "roofline": roofline, "kernels": kernels,
-        "stage_ms": {"coarse_total": stage_ms[0], "fine_gather": stage_ms[1], "fine_transformer": ft_ms,
-                     "fine_match": stage_ms[2], "pack_and_gather": stage_ms[3]},
+        "stage_ms": {"coarse_transformer": ct_ms, "coarse_total": stage_ms[0], "fine_gather": stage_ms[1],
+                     "fine_transformer": ft_ms, "fine_match": stage_ms[2], "pack_and_gather": stage_ms[3]},
         "e2e": e2e, "gpu_launches": K * (LAUNCHES_PER_STEP + (4 if args.with_fine_transformer else 0)), "clocks": clocks,
     }
     if world == 1 and not args.no_cpu_baseline:
