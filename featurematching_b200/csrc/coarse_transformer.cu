@@ -51,10 +51,10 @@ constexpr int kHd = 32;                // head dimension
 constexpr int kTM = 128;               // rows per tile
 constexpr int kTN = 256;               // columns per tile
 constexpr int kBK = 64;                // K per stage (one 128-byte swizzle row of bf16)
-constexpr int kStages = 2;
-constexpr int kAPlaneBytes = kTM * kBK * 2;          // 16 KB
-constexpr int kWPlaneBytes = kTN * kBK * 2;          // 32 KB
-constexpr int kStageBytes = 2 * kAPlaneBytes + 2 * kWPlaneBytes;   // 96 KB
+constexpr int kStages = 3;
+constexpr int kAPlaneBytes = kTM * kBK * 2;          // 16 KB: this CTA's 128 rows of the pair's 256-row A tile
+constexpr int kWPlaneBytes = (kTN / 2) * kBK * 2;    // 16 KB: this CTA's 128 of the W tile's 256 rows (its N half)
+constexpr int kStageBytes = 2 * kAPlaneBytes + 2 * kWPlaneBytes;   // 64 KB per CTA
 constexpr int kGemmThreads = 320;      // producer warp, MMA warp, 8 epilogue warps
 constexpr int kEpiThreads = 256;
 constexpr int kKvChunk = 256;          // tokens per K'^T V partial
@@ -229,8 +229,8 @@ struct CtGemmParams {
     int KB;                   // K / 64
     int kb_split;             // K blocks [0, kb_split) come from tensor map A0, the rest from A1 (cat[x, message])
     int n_tiles;              // N / 256
-    int tiles_per_img;
-    int num_units;            // B * tiles_per_img * n_tiles, the column tile innermost
+    int tiles_per_img;        // pairs of 128-row tiles per image
+    int num_units;            // B * tiles_per_img * n_tiles (one per CTA pair), the column tile innermost
     int w_per_image;          // 1: the W operand is per image (blockdiag KV); 0: layer weights
     float* f32_a;             // kEpiKV: K' [B*L][256]
     float* f32_b;             // kEpiKV: V / S
@@ -274,7 +274,7 @@ __device__ __forceinline__ void store_planes32(__nv_bfloat16* dst, size_t plane_
 }
 
 template <int kEpi>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 ct_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
                const __grid_constant__ CUtensorMap mapW, const CtGemmParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -285,7 +285,8 @@ ct_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(&ctl->t_full[s], 1); mbar_init(&ctl->t_empty[s], kEpiThreads / 32); }
+        // t_empty lives in the leader CTA: the epilogue warps of BOTH CTAs arrive on it
+        for (int s = 0; s < 2; ++s) { mbar_init(&ctl->t_full[s], 1); mbar_init(&ctl->t_empty[s], 2 * kEpiThreads / 32); }
         fence_mbar_init();
         tma_prefetch_desc(&mapA0);
         tma_prefetch_desc(&mapA1);
@@ -293,42 +294,49 @@ ct_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
     }
     if (kNorm)
         for (int i = threadIdx.x; i < 2 * kD; i += kGemmThreads) ctl->lnp[i] = p.ln[i];
-    if (warp == 0) tmem_alloc<512>(&ctl->tmem_base);
+    if (warp == 0) tmem_alloc_pair<512>(&ctl->tmem_base);
     tc_fence_before();
     __syncthreads();
+    cluster_sync_all();   // the peer's barriers are initialised before anything signals them
     tc_fence_after();
     const uint32_t tmem_base = ctl->tmem_base;
+    // A CTA PAIR works on one unit: 256 rows (two row tiles of ONE image; rank r takes tile 2 i + r, which
+    // may lie past the image's end: all its rows are then zero-filled by TMA and never stored) x 256 columns.
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
 
     if (warp == 0) {
-        // ===================================================== TMA producer (one lane)
+        // ===================================================== TMA producer (one lane, both CTAs)
         if (lane == 0) {
             uint32_t it = 0;
-            for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
+            for (int u = pair; u < p.num_units; u += npairs) {
                 const int nt = u % p.n_tiles, t = u / p.n_tiles;
-                const int b = t / p.tiles_per_img, r0 = (t % p.tiles_per_img) * kTM;
+                const int b = t / p.tiles_per_img, r0 = ((t % p.tiles_per_img) * 2 + rank) * kTM;
                 const int g = p.w_per_image ? b : 0;
                 for (int kb = 0; kb < p.KB; ++kb, ++it) {
                     const uint32_t s = it % kStages, ph = (it / kStages) & 1;
                     mbar_wait(&ctl->empty[s], ph ^ 1);
-                    mbar_arrive_expect_tx(&ctl->full[s], kStageBytes);
+                    // both CTAs' loads complete on the LEADER's barrier, which expects the pair's bytes
+                    if (rank == 0) mbar_arrive_expect_tx(&ctl->full[s], 2 * kStageBytes);
                     uint8_t* st = smem + static_cast<size_t>(s) * kStageBytes;
                     const bool first = kb < p.kb_split;
                     const CUtensorMap* ma = first ? &mapA0 : &mapA1;
                     const int kk = (first ? kb : kb - p.kb_split) * kBK;
-                    tma_load_4d(st, ma, &ctl->full[s], kk, r0, b, 0);
-                    tma_load_4d(st + kAPlaneBytes, ma, &ctl->full[s], kk, r0, b, 1);
-                    tma_load_4d(st + 2 * kAPlaneBytes, &mapW, &ctl->full[s], kb * kBK, nt * kTN, 0, g);
-                    tma_load_4d(st + 2 * kAPlaneBytes + kWPlaneBytes, &mapW, &ctl->full[s], kb * kBK, nt * kTN, 1, g);
+                    const int n0 = nt * kTN + static_cast<int>(rank) * (kTN / 2);
+                    tma_load_4d_pair(st, ma, &ctl->full[s], kk, r0, b, 0);
+                    tma_load_4d_pair(st + kAPlaneBytes, ma, &ctl->full[s], kk, r0, b, 1);
+                    tma_load_4d_pair(st + 2 * kAPlaneBytes, &mapW, &ctl->full[s], kb * kBK, n0, 0, g);
+                    tma_load_4d_pair(st + 2 * kAPlaneBytes + kWPlaneBytes, &mapW, &ctl->full[s], kb * kBK, n0, 1, g);
                 }
             }
         }
     } else if (warp == 1) {
         // ===================================================== MMA issuer (one lane)
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16_f32(kTM, kTN);
+        if (lane == 0 && rank == 0) {   // the leader CTA issues the pair's MMAs
+            constexpr uint32_t idesc = umma_idesc_bf16_f32(2 * kTM, kTN);
             const uint32_t smem_base = smem_u32(smem);
             uint32_t it = 0, tile_it = 0;
-            for (int u = blockIdx.x; u < p.num_units; u += gridDim.x, ++tile_it) {
+            for (int u = pair; u < p.num_units; u += npairs, ++tile_it) {
                 const uint32_t buf = tile_it & 1, tph = (tile_it >> 1) & 1;
                 mbar_wait(&ctl->t_empty[buf], tph ^ 1);
                 tc_fence_after();
@@ -344,12 +352,12 @@ ct_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
                         const uint32_t a = term == 2 ? a_lo : a_hi, w = term == 1 ? w_lo : w_hi;
 #pragma unroll
                         for (int k = 0; k < kBK / 16; ++k)
-                            umma_bf16_ss(d_tmem, umma_desc_k_sw128(a + k * 32), umma_desc_k_sw128(w + k * 32), idesc,
-                                         (kb | term | k) != 0 ? 1u : 0u);
+                            umma_bf16_ss_pair(d_tmem, umma_desc_k_sw128(a + k * 32), umma_desc_k_sw128(w + k * 32), idesc,
+                                              (kb | term | k) != 0 ? 1u : 0u);
                     }
-                    umma_commit(&ctl->empty[s]);   // frees the stage once these MMAs retire
+                    umma_commit_pair(&ctl->empty[s]);   // frees the stage in both CTAs once these MMAs retire
                 }
-                umma_commit(&ctl->t_full[buf]);    // accumulator complete
+                umma_commit_pair(&ctl->t_full[buf]);    // accumulator complete (both CTAs' epilogues)
             }
         }
     } else {
@@ -358,9 +366,9 @@ ct_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
         const int g = (warp - 2) >> 2;        // column half
         const int rl = q * 32 + lane;         // row within the tile
         uint32_t tile_it = 0;
-        for (int u = blockIdx.x; u < p.num_units; u += gridDim.x, ++tile_it) {
+        for (int u = pair; u < p.num_units; u += npairs, ++tile_it) {
             const int nt = u % p.n_tiles, t = u / p.n_tiles;
-            const int b = t / p.tiles_per_img, row = (t % p.tiles_per_img) * kTM + rl;
+            const int b = t / p.tiles_per_img, row = ((t % p.tiles_per_img) * 2 + static_cast<int>(rank)) * kTM + rl;
             const bool valid = row < p.L;
             const size_t gr = static_cast<size_t>(b) * p.L + row;
             const uint32_t buf = tile_it & 1, tph = (tile_it >> 1) & 1;
@@ -492,14 +500,15 @@ ct_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
             // release the accumulator buffer to the MMA warp
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&ctl->t_empty[buf]);
+            if (lane == 0) mbar_arrive_cluster(&ctl->t_empty[buf], 0);
         }
     }
 
     tc_fence_before();
     __syncthreads();
+    cluster_sync_all();   // the peer may still be reading operands / signalling barriers of this CTA
     tc_fence_after();
-    if (warp == 0) tmem_dealloc<512>(tmem_base);
+    if (warp == 0) tmem_dealloc_pair<512>(tmem_base);
 }
 
 // ---------------------------------------------------------------- host: workspace plan and launches
@@ -542,12 +551,12 @@ bool make_act_map(CUtensorMap* m, const void* ptr, int K, int L, int B) {
     const uint32_t box[4] = {kBK, kTM, 1, 1};
     return encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, ptr, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
 }
-// weight planes [G][2][N][K] bf16 as (K, N, plane, G); box 64 x 256 rows
+// weight planes [G][2][N][K] bf16 as (K, N, plane, G); box 64 x 128 rows
 bool make_w_map(CUtensorMap* m, const void* ptr, int K, int N, int G) {
     const uint64_t dims[4] = {static_cast<uint64_t>(K), static_cast<uint64_t>(N), 2, static_cast<uint64_t>(G)};
     const uint64_t strides[3] = {static_cast<uint64_t>(K) * 2, static_cast<uint64_t>(N) * K * 2,
                                  2ull * N * K * 2};
-    const uint32_t box[4] = {kBK, kTN, 1, 1};
+    const uint32_t box[4] = {kBK, kTN / 2, 1, 1};   // a CTA of the pair loads its half of the 256-row tile
     return encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, ptr, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
@@ -563,10 +572,10 @@ cudaError_t launch_gemm(const CUtensorMap& a0, const CUtensorMap& a1, const CUte
     }
     p.KB = K / kBK;
     p.n_tiles = N / kTN;
-    p.tiles_per_img = (p.L + kTM - 1) / kTM;
+    p.tiles_per_img = ((p.L + kTM - 1) / kTM + 1) / 2;   // PAIRS of row tiles per image (the last may be half empty)
     p.num_units = p.B * p.tiles_per_img * p.n_tiles;
     if (p.num_units == 0) return cudaSuccess;
-    const int grid = std::min(num_sms, p.num_units);
+    const int grid = 2 * std::min(num_sms / 2, p.num_units);   // whole CTA pairs
     ct_gemm_kernel<kEpi><<<grid, kGemmThreads, kGemmSmem, st>>>(a0, a1, w, p);
     return cudaGetLastError();
 }
