@@ -57,7 +57,7 @@ constexpr int kWPlaneBytes = (kTN / 2) * kBK * 2;    // 16 KB: this CTA's 128 of
 constexpr int kStageBytes = 2 * kAPlaneBytes + 2 * kWPlaneBytes;   // 64 KB per CTA
 constexpr int kGemmThreads = 320;      // producer warp, MMA warp, 8 epilogue warps
 constexpr int kEpiThreads = 256;
-constexpr int kKvChunk = 256;          // tokens per K'^T V partial
+constexpr int kKvChunkMin = 64;        // fewest tokens per K'^T V partial (bounds the partial buffers)
 
 // ---- per-layer weight blob (bf16 planes [hi, lo], plain row-major [N][K]; TMA applies the swizzle)
 constexpr size_t kWqOff = 0;                                   // [2][256][256]
@@ -123,53 +123,66 @@ __global__ void __launch_bounds__(256) ct_split_kernel(const float4* __restrict_
 
 // ---------------------------------------------------------------- K'^T V (attentions.py:42-43)
 // grid (chunks, B); one warp per head; a lane owns a 4 (d) x 8 (v) patch of the head's 32 x 32
-// matrix.  Tokens stream through shared memory 16 at a time, the next 16 already in flight in
-// registers; the products are packed f32x2 FMAs.  Partial sums per (image, chunk) are written, not
-// accumulated atomically, so the result does not depend on scheduling.
-__global__ void __launch_bounds__(256) ct_kv_partial_kernel(const float* __restrict__ kf, const float* __restrict__ vf,
-                                                            int L, float* __restrict__ kvpart,
-                                                            float* __restrict__ kspart) {
-    __shared__ __align__(16) float sk[16][kD];
-    __shared__ __align__(16) float sv[16][kD];
+// matrix.  Tokens stream through a 3-stage cp.async ring in shared memory, 16 tokens (32 KB of K' | V) per
+// stage, so two stages are always in flight per CTA (an HBM-bound streaming read); the products are
+// packed f32x2 FMAs.  Partial sums per (image, chunk) are written, not accumulated atomically, so the result
+// does not depend on scheduling.
+constexpr int kKvStages = 3;
+constexpr int kKvStageTokens = 16;
+constexpr int kKvSmem = kKvStages * 2 * kKvStageTokens * kD * 4;   // 96 KB
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int kPending>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory"); }
+
+__global__ void __launch_bounds__(256, 2) ct_kv_partial_kernel(const float* __restrict__ kf, const float* __restrict__ vf,
+                                                               int L, int chunk_tokens, float* __restrict__ kvpart,
+                                                               float* __restrict__ kspart) {
+    extern __shared__ __align__(16) uint8_t kv_smem[];
+    float* ring = reinterpret_cast<float*>(kv_smem);   // [stage][K' | V][16 tokens][256]
     const int chunk = blockIdx.x, b = blockIdx.y, nchunks = gridDim.x;
     const int h = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int dg = lane >> 2, vg = lane & 3;
-    const int t0 = chunk * kKvChunk, t1 = min(t0 + kKvChunk, L);
+    const int t0 = min(chunk * chunk_tokens, L), t1 = min(t0 + chunk_tokens, L);
+    const int nblk = (t1 - t0 + kKvStageTokens - 1) / kKvStageTokens;
     uint64_t acc[4][4];   // [d][v pair]
     uint64_t ks[2] = {0ull, 0ull};
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j] = 0ull;
-    float4 pk[4], pv[4];
-    auto fetch = [&](int t) {
-        const int n4 = min(16, t1 - t) * (kD / 4);
-        const float4* gk = reinterpret_cast<const float4*>(kf + (static_cast<size_t>(b) * L + t) * kD);
-        const float4* gv = reinterpret_cast<const float4*>(vf + (static_cast<size_t>(b) * L + t) * kD);
+    auto issue = [&](int blk) {   // one commit group per block, empty past the end (keeps the group count uniform)
+        if (blk < nblk) {
+            const int t = t0 + blk * kKvStageTokens;
+            const int n4 = min(kKvStageTokens, t1 - t) * (kD / 4);
+            float* sk = ring + static_cast<size_t>(blk % kKvStages) * 2 * kKvStageTokens * kD;
+            float* sv = sk + kKvStageTokens * kD;
+            const float4* gk = reinterpret_cast<const float4*>(kf + (static_cast<size_t>(b) * L + t) * kD);
+            const float4* gv = reinterpret_cast<const float4*>(vf + (static_cast<size_t>(b) * L + t) * kD);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int e = threadIdx.x + i * 256;
-            if (e < n4) { pk[i] = __ldg(gk + e); pv[i] = __ldg(gv + e); }
-        }
-    };
-    if (t0 < t1) fetch(t0);
-    for (int t = t0; t < t1; t += 16) {
-        const int nt = min(16, t1 - t);
-        __syncthreads();
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int e = threadIdx.x + i * 256;
-            if (e < nt * (kD / 4)) {
-                reinterpret_cast<float4*>(&sk[0][0])[e] = pk[i];
-                reinterpret_cast<float4*>(&sv[0][0])[e] = pv[i];
+            for (int i = 0; i < 4; ++i) {
+                const int e = threadIdx.x + i * 256;
+                if (e < n4) { cp_async16(sk + e * 4, gk + e); cp_async16(sv + e * 4, gv + e); }
             }
         }
-        __syncthreads();
-        if (t + 16 < t1) fetch(t + 16);
+        cp_async_commit();
+    };
+    issue(0);
+    issue(1);
+    for (int blk = 0; blk < nblk; ++blk) {
+        cp_async_wait<1>();   // block blk has landed (this thread's part); the barrier publishes everyone's
+        __syncthreads();      // ... and everyone is done with the stage block blk + 2 will overwrite
+        issue(blk + 2);
+        const int nt = min(kKvStageTokens, t1 - (t0 + blk * kKvStageTokens));
+        const float* sk = ring + static_cast<size_t>(blk % kKvStages) * 2 * kKvStageTokens * kD;
+        const float* sv = sk + kKvStageTokens * kD;
         for (int r = 0; r < nt; ++r) {
-            const float4 k4 = *reinterpret_cast<const float4*>(&sk[r][h * kHd + dg * 4]);
-            const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(&sv[r][h * kHd + vg * 8]);
-            const ulonglong2 vb = *reinterpret_cast<const ulonglong2*>(&sv[r][h * kHd + vg * 8 + 4]);
+            const float4 k4 = *reinterpret_cast<const float4*>(sk + r * kD + h * kHd + dg * 4);
+            const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(sv + r * kD + h * kHd + vg * 8);
+            const ulonglong2 vb = *reinterpret_cast<const ulonglong2*>(sv + r * kD + h * kHd + vg * 8 + 4);
             ks[0] = add2(ks[0], pack2(k4.x, k4.y));
             ks[1] = add2(ks[1], pack2(k4.z, k4.w));
             const float kk[4] = {k4.x, k4.y, k4.z, k4.w};
@@ -183,6 +196,7 @@ __global__ void __launch_bounds__(256) ct_kv_partial_kernel(const float* __restr
             }
         }
     }
+    cp_async_wait<0>();
     float* out = kvpart + ((static_cast<size_t>(b) * nchunks + chunk) * kH + h) * (kHd * kHd);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -522,7 +536,7 @@ struct CtPlan {
 CtPlan ct_plan(int B, int L0, int L1, int n_layers) {
     CtPlan pl{};
     const size_t Lm = static_cast<size_t>(std::max(L0, L1)), R = static_cast<size_t>(B) * Lm;
-    pl.chunks_max = static_cast<int>((Lm + kKvChunk - 1) / kKvChunk);
+    pl.chunks_max = static_cast<int>((Lm + kKvChunkMin - 1) / kKvChunkMin);
     size_t off = 0;
     auto take = [&](size_t bytes) { const size_t o = off; off = align_up(off + bytes); return o; };
     pl.blobs = take(static_cast<size_t>(n_layers) * kLayerBlobBytes);
@@ -643,6 +657,11 @@ cudaError_t launch_coarse_transformer(const float* feat0, const float* feat1, in
              make_act_map(&m_m[s], mp, kD, Ls[s], B) && make_act_map(&m_m2[s], m2p, kD, Ls[s], B) &&
              make_act_map(&m_h[s], hp, 2 * kD, Ls[s], B);
     }
+    static bool kv_attr = false;
+    if (!kv_attr) {
+        if ((e = cudaFuncSetAttribute(ct_kv_partial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kKvSmem)) != cudaSuccess) return e;
+        kv_attr = true;
+    }
     if (!ok) {
         set_error("cuTensorMapEncodeTiled failed (coarse transformer)");
         return cudaErrorInvalidValue;
@@ -672,8 +691,15 @@ cudaError_t launch_coarse_transformer(const float* feat0, const float* feat1, in
             p.L = S; p.kb_split = 4; p.w_per_image = 0; p.f32_a = kf; p.f32_b = vf;
             if ((e = launch_gemm<kEpiKV>(m_x[ss], m_x[ss], w_kv, p, kD, 2 * kD, num_sms, st)) != cudaSuccess) return e;
             // 2. K'^T V
-            const int chunks = (S + kKvChunk - 1) / kKvChunk;
-            ct_kv_partial_kernel<<<dim3(chunks, B), 256, 0, st>>>(kf, vf, S, kvpart, kspart);
+            // chunks of ~192 tokens, their number trimmed so that B x chunks fills whole waves of 2 CTAs per SM
+            int chunks = (S + 191) / 192;
+            {
+                const int slots = 2 * num_sms, waves = std::max(1, (B * chunks + slots / 2) / slots);
+                chunks = std::max(1, std::min((S + kKvChunkMin - 1) / kKvChunkMin, std::max(chunks / 2, waves * slots / B)));
+            }
+            const int chunk_tokens = (S + chunks - 1) / chunks;
+            chunks = (S + chunk_tokens - 1) / chunk_tokens;
+            ct_kv_partial_kernel<<<dim3(chunks, B), 256, kKvSmem, st>>>(kf, vf, S, chunk_tokens, kvpart, kspart);
             ct_kv_finalize_kernel<<<dim3(kH, B), 256, 0, st>>>(kvpart, kspart, chunks, kvbd, ksum);
             // 3. Q', Z
             p.L = Lx; p.planes = qp; p.plane_stride = Rx * kD; p.ld = kD; p.ksum = ksum; p.z = z;

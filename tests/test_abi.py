@@ -106,6 +106,31 @@ def test_fine_transformer_argument_errors(lib):
         assert call() == -3 and b"no CUDA device" in lib.fm_last_error_string()
 
 
+def test_coarse_transformer_argument_errors(lib):
+    buf = (ctypes.c_char * 4096)()
+    p = ctypes.c_void_p((ctypes.addressof(buf) + 255) & ~255)
+    kinds = (ctypes.c_int32 * 2)(0, 1)
+    ptrs = (ctypes.c_void_p * 20)(*[p.value] * 20)
+    need = lib.fm_coarse_transformer_workspace_bytes(2, 300, 200, 2)
+    # two layers of packed weights (2.5 MB each) + operand planes for 2 x 500 tokens
+    assert need > 2 * 2_600_000 + 2 * 500 * 1024 and lib.fm_coarse_transformer_workspace_bytes(2, 300, 200, 0) == 0
+    assert lib.fm_coarse_transformer_workspace_bytes(32, 5120, 5120, 8) < 4 << 30     # the 640x512 batch: < 4 GB
+    call = lambda B=2, L0=300, L1=200, C=256, nhead=8, ws=need, k=kinds, pp=ptrs, w=p, f0=p: lib.fm_coarse_transformer(
+        f0, p, B, L0, L1, C, nhead, 2, k, pp, p, p, None, None, w, ws, None)
+    assert call(C=64) == -4 and b"d_model 256" in lib.fm_last_error_string()       # FM_ERR_UNSUPPORTED
+    assert call(nhead=4) == -4
+    assert call(ws=need - 1) == -2                                                  # FM_ERR_WORKSPACE
+    assert call(k=(ctypes.c_int32 * 2)(0, 7)) == -1                                 # bad layer kind
+    bad = (ctypes.c_void_p * 20)(*([p.value] * 19 + [None]))
+    assert call(pp=bad) == -1                                                       # NULL parameter pointer
+    assert call(f0=None) == -1                                                      # NULL tokens with B * L0 > 0
+    assert call(w=ctypes.c_void_p(p.value + 32)) == -1 and b"256-byte" in lib.fm_last_error_string()
+    assert call(f0=ctypes.c_void_p(p.value + 8)) == -1                              # 32-byte alignment of the tokens
+    assert call(B=0) == 0 and call(L0=0, L1=0) == 0                                 # nothing to do
+    if not torch.cuda.is_available():
+        assert call() == -3 and b"no CUDA device" in lib.fm_last_error_string()
+
+
 def test_transformer_module_keeps_reference_state_dict_keys():
     """modules.LocalFeatureTransformer loads a reference fine-transformer state dict strictly
     (network/module/transformer.py:59-76 parameter names) and refuses CPU tensors."""
@@ -126,3 +151,39 @@ def test_transformer_module_keeps_reference_state_dict_keys():
         m.eval()(torch.zeros(1, 49, 64), torch.zeros(1, 49, 64))
     with pytest.raises(_lib.FmError):
         modules.LocalFeatureTransformer(dict(cfg, attention="full"))
+
+
+@pytest.mark.skipif(not __import__("oracle.reference_shims", fromlist=["x"]).available(), reason="reference tree not present")
+def test_install_swaps_the_five_modules_and_keeps_the_state_dict():
+    """modules.install on a holder built from the reference's own sub-modules (network/net.py:24-38 without
+    the backbone): every hot-path attribute is replaced, state-dict keys and values are unchanged."""
+    from featurematching_b200 import modules
+    from oracle import reference_shims
+    ref = reference_shims.load_reference()
+    cfg = reference_shims.default_config()
+
+    class Holder(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.config = cfg
+            self.coarse = ref.LocalFeatureTransformer(cfg["coarse"])
+            self.coarse_matching = ref.CoarseMatching(cfg["match_coarse"])
+            self.fine_preprocess = ref.FinePreprocess(cfg)
+            self.fine = ref.LocalFeatureTransformer(cfg["fine"])
+            self.fine_matching = ref.FineMatching(cfg["fine"])
+
+    torch.manual_seed(3)
+    net = Holder()
+    before = {k: v.clone() for k, v in net.state_dict().items()}
+    modules.install(net)
+    for name, cls in (("coarse", modules.LocalFeatureTransformer), ("coarse_matching", modules.CoarseMatching),
+                      ("fine_preprocess", modules.FinePreprocess), ("fine", modules.LocalFeatureTransformer),
+                      ("fine_matching", modules.FineMatching)):
+        assert isinstance(getattr(net, name), cls), name
+    after = net.state_dict()
+    assert set(k for k in before if not k.startswith("coarse_matching")) <= set(after)
+    for k, v in before.items():
+        if k in after:
+            assert torch.equal(after[k], v), k
+    assert set(net._fm_reference) == {"coarse", "coarse_matching", "fine_preprocess", "fine", "fine_matching"}
+    assert not net.training
