@@ -209,9 +209,23 @@ def cpu_baseline(args):
         el = time.perf_counter() - t0
         if el >= args.cpu_seconds or n >= args.pairs:
             break
-    return {"value": n / el, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{n} of the {args.pairs} pairs of one step ({matches // n} matches/pair), oracle "
-                      f"match head (torch CPU fp32, {cores} threads), {el:.1f} s"}
+    out = {"value": n / el, "unit": UNIT, "cores": cores, "kind": "port",
+           "sample": f"{n} of the {args.pairs} pairs of one step ({matches // n} matches/pair), oracle "
+                     f"match head (torch CPU fp32, {cores} threads), {el:.1f} s"}
+    if not args.no_coarse_transformer:
+        # the coarse transformer stage beside it: the oracle's restatement on ONE pair of the same token count
+        import torch
+        from oracle import matcher_oracle as mo
+        _, _, _, N = shapes(args)
+        layers = mo.transformer_params_from_state_dict(coarse_transformer_module().state_dict(), len(COARSE_CFG["layer_names"]))
+        f0, f1 = mo.seeded_tokens(5, 1, N, N, 256)
+        with torch.no_grad():
+            t0 = time.perf_counter()
+            mo.local_feature_transformer(f0, f1, layers, COARSE_CFG["layer_names"], COARSE_CFG["nhead"])
+            ct = time.perf_counter() - t0
+        out["coarse_transformer"] = {"value": 1.0 / ct, "unit": UNIT, "ms_per_pair": 1e3 * ct,
+                                     "sample": f"1 pair of 2 x {N} tokens, 8 layers, oracle (torch CPU fp32, {cores} threads)"}
+    return out
 
 
 def run_reference(args):
