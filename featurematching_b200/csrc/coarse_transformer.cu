@@ -647,7 +647,6 @@ cudaError_t launch_coarse_transformer(const float* feat0, const float* feat1, in
                                               reinterpret_cast<uint2*>(xp[s] + static_cast<size_t>(B) * Ls[s] * kD), n4);
     }
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    if (L0 == 0 || L1 == 0 || B == 0) return cudaSuccess;   // an empty sequence leaves the other side's tokens as they are
 
     // tensor maps of the activation buffers (the intermediate ones depend on the x side's length)
     CUtensorMap m_x[2], m_q[2], m_m[2], m_m2[2], m_h[2], m_kv;

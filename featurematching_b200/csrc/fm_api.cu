@@ -513,6 +513,10 @@ int fm_coarse_transformer(const float* feat0, const float* feat1, int B, int L0,
         return FM_ERR_WORKSPACE;
     }
     if (B == 0 || (L0 == 0 && L1 == 0)) return FM_OK;
+    if (L0 == 0 || L1 == 0) {   // attentions.py:40-41 divides by the source length: the reference yields NaN here
+        set_error("coarse transformer: one sequence is empty (L0=%d, L1=%d)", L0, L1);
+        return FM_ERR_BAD_ARG;
+    }
     const int sms = sm_count();
     if (sms <= 0) { set_error("no CUDA device available (this library has no CPU path)"); return FM_ERR_CUDA; }
     cudaError_t e = launch_coarse_transformer(feat0, feat1, B, L0, L1, n_layers, layer_kinds,

@@ -181,7 +181,8 @@ FM_API int fm_fine_transformer(const float* win0, const float* win1, const int32
  * coarse config, demo/net_config.py:20-25).  layer_kinds / layer_params as for fm_fine_transformer.
  * workspace: fm_coarse_transformer_workspace_bytes(B, L0, L1, n_layers) bytes, 256-byte aligned;
  * token pointers 32-byte aligned.  All GEMMs run on the tensor cores with fp32-grade 3-term bf16
- * splits.  An empty side (L == 0) leaves the other side's tokens unchanged (copied to out). */
+ * splits.  B == 0 or L0 == L1 == 0 is a no-op; exactly one empty side is FM_ERR_BAD_ARG (the reference
+ * divides by the source length, attentions.py:40-41). */
 FM_API size_t fm_coarse_transformer_workspace_bytes(int B, int L0, int L1, int n_layers);
 FM_API int fm_coarse_transformer(const float* feat0, const float* feat1, int B, int L0, int L1, int C,
                           int nhead, int n_layers, const int32_t* layer_kinds,

@@ -127,6 +127,7 @@ def test_coarse_transformer_argument_errors(lib):
     assert call(w=ctypes.c_void_p(p.value + 32)) == -1 and b"256-byte" in lib.fm_last_error_string()
     assert call(f0=ctypes.c_void_p(p.value + 8)) == -1                              # 32-byte alignment of the tokens
     assert call(B=0) == 0 and call(L0=0, L1=0) == 0                                 # nothing to do
+    assert call(L1=0) == -1 and b"empty" in lib.fm_last_error_string()                # the reference divides by S
     if not torch.cuda.is_available():
         assert call() == -3 and b"no CUDA device" in lib.fm_last_error_string()
 
