@@ -84,6 +84,8 @@ def test_coarse_transformer_kernel_matches_reference_golden(golden_dir):
     (3, 300, 257, ["self", "cross"]),
     (2, 1, 5, ["cross", "self"]),
     (2, 640, 520, ["self", "cross"] * 4),
+    (1, 5120, 5120, ["self", "cross"] * 4),      # one full-size 640x512 pair, the shipped 8 layers
+    (3, 1600, 1600, ["cross", "self"]),          # 320x320 frames, 12.5 tile pairs per image
 ])
 def test_coarse_transformer_kernel_vs_oracle(B, L0, L1, names):
     layers = mo.seeded_transformer_layers(100 + L0, 256, len(names))
