@@ -14,7 +14,7 @@ DTYPE_BF16, DTYPE_F32 = 0, 1
 STATUS_WORDS = 8
 RECORD_BYTES = 40
 MAX_CHUNKS = 64
-ST_COUNT, ST_FLAGS, ST_MAX_CAND, ST_LOST, ST_CAND_TOTAL = 0, 1, 2, 3, 4
+ST_COUNT, ST_FLAGS, ST_MAX_CAND, ST_LOST, ST_CAND_TOTAL, ST_REDO = 0, 1, 2, 3, 4, 5
 FLAG_CAND_OVERFLOW, FLAG_OUT_OVERFLOW, FLAG_TIE_OVERFLOW, FLAG_RANGE = 1, 2, 4, 8
 
 _c = ctypes

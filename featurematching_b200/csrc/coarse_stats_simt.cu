@@ -101,13 +101,12 @@ cudaError_t launch_coarse_stats_simt(const __nv_bfloat16* f0, const __nv_bfloat1
                                      const CoarseStatsParams& p, cudaStream_t st) {
     const CoarseDims& d = p.d;
     const size_t smem = static_cast<size_t>(2) * kT * (d.C + 2) * sizeof(__nv_bfloat16);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_set = 0;
+    if (needs_attr_on_this_device(&attr_set)) {
         cudaError_t e = cudaFuncSetAttribute(coarse_stats_simt_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(coarse_stats_simt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024);
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     cudaError_t e = cudaMemsetAsync(p.rowpart, 0, sizeof(float) * d.B * d.NB * 2 * d.N0pad, st);
     if (e != cudaSuccess) return e;

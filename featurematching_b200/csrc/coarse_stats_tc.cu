@@ -57,11 +57,14 @@ constexpr size_t kSmemOperands = static_cast<size_t>(kBChunkBytes) * kKC +
 constexpr size_t kSmemBytes = kSmemOperands + sizeof(SmemCtl) + 1024;  // + alignment slack
 static_assert(kSmemBytes <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
 
-// One 32-column chunk of the thread's accumulator row; returns the chunk's largest p.
+// One 32-column chunk of the thread's accumulator row.  Returns the chunk's largest p (first pass) or, in the
+// exact pass (kExact; `lc` = log2 column soft-max sums of the chunk's 32 columns), its largest
+// 2 log2(p) - l2col_j = log2(conf_ij) + (l2row_i - 2 c_i): the confidence itself up to a per-row constant.
+template <bool kExact>
 __device__ __forceinline__ float process_chunk(const uint32_t (&r)[32], uint64_t a2p, uint64_t biasp,
                                                uint64_t wp, uint64_t* colacc, uint64_t& racc0,
-                                               uint64_t& racc1) {
-    float m = 0.f;
+                                               uint64_t& racc1, const float* __restrict__ lc) {
+    float m = kExact ? -INFINITY : 0.f;
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
         uint64_t t2 = fma2(pack2(__uint_as_float(r[2 * k]), __uint_as_float(r[2 * k + 1])), a2p, biasp);
@@ -71,7 +74,8 @@ __device__ __forceinline__ float process_chunk(const uint32_t (&r)[32], uint64_t
         const uint64_t p2 = pack2(pl, ph);
         if (k & 1) racc1 = add2(racc1, p2); else racc0 = add2(racc0, p2);
         colacc[k] = fma2(p2, wp, colacc[k]);
-        m = max3(m, pl, ph);
+        if (kExact) m = max3(m, fmaf(2.f, tl, -__ldg(lc + 2 * k)), fmaf(2.f, th, -__ldg(lc + 2 * k + 1)));
+        else m = max3(m, pl, ph);
     }
     return m;
 }
@@ -97,6 +101,8 @@ __device__ __forceinline__ void reduce_step(float* v, int lane) {
     }
 }
 
+// kExact = the second extraction pass (see CoarseStatsParams::l2row): same sums, exact hot-chunk test.
+template <bool kExact>
 __global__ void __launch_bounds__(kCoarseThreads, 1)
 coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                        const __grid_constant__ CUtensorMap tmap1, const CoarseStatsParams p) {
@@ -109,6 +115,7 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
     const CoarseDims& d = p.d;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int KC = d.KC;
+    if (kExact && p.redo && *p.redo == 0) return;   // exact pass not needed (uniform over the grid)
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kAStages; ++s) { mbar_init(&ctl->a_full[s], 1); mbar_init(&ctl->a_empty[s], 1); }
@@ -222,6 +229,11 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
             // token norm of this thread's row, fetched one tile ahead (N0pad rows exist)
             const float* norm_b = p.norm0 + static_cast<size_t>(b) * d.N0pad + q * 32 + lane;
             float n0_next = __ldg(norm_b + mt0 * kTileM);
+            // exact pass: log2 soft-max sums of this pair's rows and of this warpgroup's 128 columns (the l2col
+            // buffer has kBlockN floats of slack, columns >= N1 carry p = 0 and can never be hot)
+            const float* l2row_b = kExact ? p.l2row + static_cast<size_t>(b) * d.N0 : nullptr;
+            const float* lcol = kExact ? p.l2col + static_cast<size_t>(b) * d.N1 + col0 : nullptr;
+            const float log2_cand = kExact ? log2f(p.cand_thr) : 0.f;
             for (int mt = mt0; mt < mt1; ++mt, ++tile_it) {
                 const uint32_t buf = tile_it & 1, tph = (tile_it >> 1) & 1;
                 const int row = mt * kTileM + q * 32 + lane;
@@ -245,21 +257,21 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                 tmem_ld_wait_dep(ra);
                 tmem_ld_32x32(taddr + 32, rb);
                 if (nvalid < 32) mask_chunk(ra, nvalid);
-                cm[0] = process_chunk(ra, a2p, biasp, wp, colacc, racc0, racc1);
+                cm[0] = process_chunk<kExact>(ra, a2p, biasp, wp, colacc, racc0, racc1, lcol + 0);
                 // chunk 1
                 tmem_ld_wait_dep(rb);
                 tmem_ld_32x32(taddr + 64, ra);
                 if (nvalid < 64) mask_chunk(rb, nvalid - 32);
-                cm[1] = process_chunk(rb, a2p, biasp, wp, colacc + 16, racc0, racc1);
+                cm[1] = process_chunk<kExact>(rb, a2p, biasp, wp, colacc + 16, racc0, racc1, lcol + 32);
                 // chunk 2
                 tmem_ld_wait_dep(ra);
                 tmem_ld_32x32(taddr + 96, rb);
                 if (nvalid < 96) mask_chunk(ra, nvalid - 64);
-                cm[2] = process_chunk(ra, a2p, biasp, wp, colacc + 32, racc0, racc1);
+                cm[2] = process_chunk<kExact>(ra, a2p, biasp, wp, colacc + 32, racc0, racc1, lcol + 64);
                 // chunk 3
                 tmem_ld_wait_dep(rb);
                 if (nvalid < 128) mask_chunk(rb, nvalid - 96);
-                cm[3] = process_chunk(rb, a2p, biasp, wp, colacc + 48, racc0, racc1);
+                cm[3] = process_chunk<kExact>(rb, a2p, biasp, wp, colacc + 48, racc0, racc1, lcol + 96);
 
                 float s0, s1, s2, s3;
                 unpack2(racc0, s0, s1);
@@ -268,7 +280,11 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                 rowpart[mt * kTileM + q * 32 + lane] = rowsum;
 
                 // ---- hot chunks: largest p above the share threshold of the row's partial sum
-                const float share = p.cand_thr * rowsum;
+                // first pass: the chunk's best p against cand_thr x the row's own 128-column partial sum (weaker
+                // than the share of the full row sum, hence a superset).  Exact pass: log2 conf_ij =
+                // (2 log2 p - l2col_j) + 2 c_i - l2row_i against log2(cand_thr); a lost row (l2row = INF) is never hot
+                const float share = kExact ? (rvalid ? log2_cand + __ldg(l2row_b + row) - 2.f * ci : INFINITY)
+                                           : p.cand_thr * rowsum;
                 uint32_t hot = 0;
 #pragma unroll
                 for (int ch = 0; ch < 4; ++ch) hot |= (cm[ch] > share) ? (1u << ch) : 0u;
@@ -380,16 +396,19 @@ cudaError_t launch_coarse_stats_tc(const __nv_bfloat16* f0, const __nv_bfloat16*
         set_error("cuTensorMapEncodeTiled failed (feature pointers must be 16-byte aligned)");
         return cudaErrorInvalidValue;
     }
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(coarse_stats_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    static unsigned long long attr_set = 0;
+    if (needs_attr_on_this_device(&attr_set)) {
+        cudaError_t e = cudaFuncSetAttribute(coarse_stats_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              static_cast<int>(kSmemBytes));
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(coarse_stats_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     static_cast<int>(kSmemBytes));
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     (void)num_sms;
     const int grid = p.d.num_pools;   // one record pool per CTA
-    coarse_stats_tc_kernel<<<grid, kCoarseThreads, kSmemBytes, st>>>(tm0, tm1, p);
+    if (p.l2row) coarse_stats_tc_kernel<true><<<grid, kCoarseThreads, kSmemBytes, st>>>(tm0, tm1, p);
+    else coarse_stats_tc_kernel<false><<<grid, kCoarseThreads, kSmemBytes, st>>>(tm0, tm1, p);
     return cudaGetLastError();
 }
 

@@ -577,12 +577,11 @@ bool make_w_map(CUtensorMap* m, const void* ptr, int K, int N, int G) {
 template <int kEpi>
 cudaError_t launch_gemm(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& w, CtGemmParams p, int K,
                         int N, int num_sms, cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_set = 0;
+    if (needs_attr_on_this_device(&attr_set)) {
         cudaError_t e = cudaFuncSetAttribute(ct_gemm_kernel<kEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              static_cast<int>(kGemmSmem));
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     p.KB = K / kBK;
     p.n_tiles = N / kTN;
@@ -656,10 +655,9 @@ cudaError_t launch_coarse_transformer(const float* feat0, const float* feat1, in
              make_act_map(&m_m[s], mp, kD, Ls[s], B) && make_act_map(&m_m2[s], m2p, kD, Ls[s], B) &&
              make_act_map(&m_h[s], hp, 2 * kD, Ls[s], B);
     }
-    static bool kv_attr = false;
-    if (!kv_attr) {
+    static unsigned long long kv_attr = 0;
+    if (needs_attr_on_this_device(&kv_attr)) {
         if ((e = cudaFuncSetAttribute(ct_kv_partial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kKvSmem)) != cudaSuccess) return e;
-        kv_attr = true;
     }
     if (!ok) {
         set_error("cuTensorMapEncodeTiled failed (coarse transformer)");

@@ -49,13 +49,13 @@ static bool timer_pair(cudaEvent_t* a, cudaEvent_t* b) {
     return true;
 }
 
-static int sm_count() {
-    static int cached = 0;
-    if (cached > 0) return cached;
+static int sm_count() {   // of the CURRENT device (cached per device)
+    static int cached[64] = {0};
     int dev = 0, n = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+    if (dev >= 0 && dev < 64 && cached[dev] > 0) return cached[dev];
     if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
-    cached = n;
+    if (dev >= 0 && dev < 64) cached[dev] = n;
     return n;
 }
 
@@ -130,14 +130,17 @@ CoarseWorkspace coarse_workspace(const CoarseDims& d, bool fp32_input, void* bas
     w.rowbest = reinterpret_cast<unsigned*>(take(sizeof(unsigned) * B * d.N0));
     w.colbest = reinterpret_cast<unsigned*>(take(sizeof(unsigned) * B * d.N1));
     w.rowcnt = reinterpret_cast<int*>(take(sizeof(int) * B * d.N0));
+    w.tie_count = reinterpret_cast<int*>(take(sizeof(int)));
+    w.redo = reinterpret_cast<int*>(take(sizeof(int)));
     w.zero_bytes = off - w.zero_begin;
     // ---- fully rewritten by every call
     w.norm0 = reinterpret_cast<float*>(take(sizeof(float) * B * d.N0pad));
     w.rowpart = reinterpret_cast<float*>(take(sizeof(float) * B * d.NB * 2 * d.N0pad));
     w.colpart = reinterpret_cast<float*>(take(sizeof(float) * B * d.S * d.N1pad));
     w.l2row = reinterpret_cast<float*>(take(sizeof(float) * B * d.N0));
-    w.l2col = reinterpret_cast<float*>(take(sizeof(float) * B * d.N1));
+    w.l2col = reinterpret_cast<float*>(take(sizeof(float) * (B * d.N1 + kBlockN)));   // slack: the exact pass reads whole blocks
     w.rowslot = reinterpret_cast<int2*>(take(sizeof(int2) * B * d.N0 * kRowSlots));
+    w.tie_list = reinterpret_cast<int4*>(take(sizeof(int4) * kTieCap));
     w.blocksum = reinterpret_cast<int*>(take(sizeof(int) * ((B * d.N0 + 1023) / 1024 + 1)));
     w.hot_meta = reinterpret_cast<uint2*>(take(sizeof(uint2) * static_cast<size_t>(d.num_pools) * d.hot_cap));
     w.hot_dots = reinterpret_cast<float*>(take(sizeof(float) * kHotChunk * static_cast<size_t>(d.num_pools) * d.hot_cap));
@@ -259,6 +262,17 @@ static int coarse_match_impl(bool simt, const void* feat_c0, const void* feat_c1
     rp.scale = scale; rp.scale0 = scale0; rp.scale1 = scale1;
     rp.b_ids = b_ids; rp.i_ids = i_ids; rp.j_ids = j_ids; rp.mconf = mconf;
     rp.mkpts0_c = mkpts0_c; rp.mkpts1_c = mkpts1_c; rp.capacity = capacity; rp.status = status;
+    // soft-max denominators; then -- only if the single-pass candidate filter overflowed (decided on the
+    // device, no host round trip) -- the statistics kernel once more, testing hot chunks against the full row sums
+    e = launch_coarse_finish_lse(rp, w, !simt, st);
+    if (e != cudaSuccess) return cuda_fail(e, "coarse_finish_lse launch");
+    if (!simt) {
+        sp.l2row = w.l2row;
+        sp.l2col = w.l2col;
+        sp.redo = w.redo;
+        e = launch_coarse_stats_tc(f0, f1, sp, sms, st);
+        if (e != cudaSuccess) return cuda_fail(e, "coarse_stats_tc (exact pass) launch");
+    }
     e = launch_coarse_resolve(rp, w, st);
     if (e != cudaSuccess) return cuda_fail(e, "coarse_resolve launch");
     return FM_OK;

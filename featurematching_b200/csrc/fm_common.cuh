@@ -20,7 +20,8 @@ constexpr int kBChunkBytes = kBlockN * kChunkK * 2;   // 32768
 constexpr int kEpiWarps = 8;
 constexpr int kCtlWarps = 4;     // warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM owner, warp 3 idle
 constexpr int kCoarseThreads = (kCtlWarps + kEpiWarps) * 32;   // 3 warpgroups: control + 2 epilogue
-constexpr int kRowSlots = 4;     // exact-tie capacity per image-0 token
+constexpr int kRowSlots = 4;     // in-row slots for exactly tied matches of one image-0 token ...
+constexpr int kTieCap = 16384;   // ... any further ones go to one shared list of (row, j, conf) entries
 
 // log2-domain head-room of the per-row exponent reference: p = 2^(t - c_i) with
 // c_i = U_i - kHead2 and U_i >= every score of the row, so p <= 2^kHead2 and sums over up to
@@ -30,7 +31,7 @@ constexpr float kHead2 = 100.0f;
 constexpr float kCandMargin = 0.9f;  // candidate pre-filter uses kCandMargin * thr
 
 // status word layout (int32[8], device): written by the coarse kernels
-enum StatusSlot { kStCount = 0, kStFlags = 1, kStMaxUnitCand = 2, kStLost = 3, kStCandTotal = 4 };
+enum StatusSlot { kStCount = 0, kStFlags = 1, kStMaxUnitCand = 2, kStLost = 3, kStCandTotal = 4, kStRedo = 5 };
 
 // Upper bound (log2 domain, slightly inflated) on every score of a token with norm n0 against
 // tokens with norm <= maxn1; used identically by the stats and resolve kernels.
@@ -69,6 +70,9 @@ struct CoarseWorkspace {
     unsigned* colbest;    // [B, N1]
     int* rowcnt;          // [B * N0]
     int2* rowslot;        // [B * N0, kRowSlots]  (j, conf bits)
+    int* tie_count;       // entries in tie_list (may exceed kTieCap: then FM_FLAG_TIE_OVERFLOW)
+    int4* tie_list;       // [kTieCap] (row, j, conf bits, 0): matches beyond a row's kRowSlots
+    int* redo;            // 1 = the single-pass candidate filter overflowed: re-extract with exact row sums
     int* blocksum;        // [ceil(B * N0 / 1024)] + scanned copy
     size_t zero_begin, zero_bytes;   // region cleared at the start of every call
     size_t total_bytes;
@@ -86,6 +90,13 @@ struct CoarseStatsParams {
     float* hot_dots;
     int* hot_count;
     int* status;
+    // Second ("exact") extraction pass, taken only when the first one overflowed its record pools: with both
+    // soft-max denominators known (finish_lse) a chunk is hot iff one of its entries has conf > cand_thr.
+    // Diffuse rows (random-init networks, thr << 1/128) make every chunk hot against a 128-column partial
+    // sum; against the confidence itself only the handful of real candidates remain.
+    const float* l2row;   // [B, N0] from finish_lse, or NULL in the first pass
+    const float* l2col;   // [B, N1] (+ kBlockN floats of slack)
+    const int* redo;      // the pass runs only if *redo != 0 (NULL: always)
 };
 
 CoarseDims coarse_dims(int B, int N0, int N1, int C, int cand_per_row, int num_sms);
@@ -111,9 +122,21 @@ struct CoarseResolveParams {
     int capacity;
     int* status;
 };
+cudaError_t launch_coarse_finish_lse(const CoarseResolveParams& p, const CoarseWorkspace& w, bool with_gate,
+                                     cudaStream_t st);
 cudaError_t launch_coarse_resolve(const CoarseResolveParams& p, const CoarseWorkspace& w,
                                   cudaStream_t st);
 
 void set_error(const char* fmt, ...);
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) belongs to a device's context: `mask` (one static per
+// kernel) remembers the devices it was set on.  True = the caller must set it for the current device.
+inline bool needs_attr_on_this_device(unsigned long long* mask) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;
+    if ((*mask >> dev) & 1ull) return false;
+    *mask |= 1ull << dev;
+    return true;
+}
 
 }  // namespace fm

@@ -83,6 +83,12 @@ class CoarseMatching(nn.Module):
                   capacity=None, out=None):
         lib = _lib.load()
         _require_cuda(feat_c0, feat_c1)
+        # tokens that come out of the B200 coarse transformer carry their bf16 rounding (written by the
+        # transformer's last epilogue, bit-equal to rn(fp32)): use it instead of casting again
+        b0, b1 = getattr(feat_c0, "_fm_bf16", None), getattr(feat_c1, "_fm_bf16", None)
+        if (b0 is not None and b1 is not None and b0.shape == feat_c0.shape and b1.shape == feat_c1.shape
+                and b0.device == feat_c0.device):
+            feat_c0, feat_c1 = b0, b1
         f0, f1 = _feat(feat_c0), _feat(feat_c1)
         if f0.dtype != f1.dtype:
             f1 = f1.to(f0.dtype)
@@ -148,8 +154,8 @@ class CoarseMatching(nn.Module):
                 capacity = raw.capacity * 4
                 continue
             if flags & _lib.FLAG_TIE_OVERFLOW:
-                raise _lib.FmError("more than 4 exactly tied coarse matches in one row "
-                                   "(duplicate descriptors); not representable")
+                raise _lib.FmError("exactly tied coarse matches beyond 4 per row exceed the shared tie list "
+                                   "(16384 entries): duplicate descriptors en masse")
             if flags & _lib.FLAG_RANGE:
                 raise _lib.FmError(
                     f"{st[_lib.ST_LOST]} tokens have all scores more than 157 nats below their "
@@ -469,7 +475,11 @@ class LocalFeatureTransformer(nn.Module):
             raise NotImplementedError("LocalFeatureTransformer (B200) is inference-only")
         with torch.no_grad():
             if self.d_model == 256:
-                return self.transform_tokens(feat0, feat1)
+                b = (torch.empty(feat0.shape, dtype=torch.bfloat16, device=feat0.device),
+                     torch.empty(feat1.shape, dtype=torch.bfloat16, device=feat1.device))
+                o0, o1 = self.transform_tokens(feat0, feat1, bf16_out=b)
+                o0._fm_bf16, o1._fm_bf16 = b   # CoarseMatching.match_raw picks these up (no second cast pass)
+                return o0, o1
             return self.transform(feat0, feat1)
 
 

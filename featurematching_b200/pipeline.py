@@ -21,6 +21,15 @@ RECORD_DTYPE = np.dtype([("pair", "<i4"), ("i", "<i4"), ("j", "<i4"), ("conf", "
 assert RECORD_DTYPE.itemsize == _lib.RECORD_BYTES
 
 
+class HeadStatusError(_lib.FmError):
+    """A device-reported condition of the coarse stage (status word of fm_coarse_match)."""
+
+    def __init__(self, flags, status):
+        super().__init__(f"coarse status flags {flags:#x} (cand overflow=1, output overflow=2, "
+                         f"tie overflow=4, range=8); status={status}")
+        self.flags, self.status = flags, status
+
+
 class HeadResult:
     """Device-side outputs of one MatchHead.run call (padded to `capacity`)."""
     __slots__ = ("coarse", "win0", "win1", "mkpts0_f", "mkpts1_f", "records", "capacity")
@@ -139,9 +148,25 @@ class MatchHead:
         st = self.coarse_matching.read_status(r.coarse)
         flags = st[_lib.ST_FLAGS]
         if flags:
-            raise _lib.FmError(f"coarse status flags {flags:#x} (cand overflow=1, output overflow=2, "
-                               f"tie overflow=4, range=8); status={st}")
+            raise HeadStatusError(flags, st)
         return st[_lib.ST_COUNT]
+
+    def run_checked(self, *args, **kwargs):
+        """run() + check_status() that repairs what can be repaired instead of raising: candidate-buffer
+        overflow (even after the on-device exact extraction pass) grows cand_per_row and runs again, output
+        overflow grows the capacity.  Returns (result, match count); one host synchronisation per attempt."""
+        while True:
+            r = self.run(*args, **kwargs)
+            try:
+                return r, self.check_status(r)
+            except HeadStatusError as e:
+                cm = self.coarse_matching
+                if e.flags & _lib.FLAG_CAND_OVERFLOW and cm.cand_per_row < 256:
+                    cm.cand_per_row = min(256, cm.cand_per_row * 4)
+                elif e.flags & _lib.FLAG_OUT_OVERFLOW and not (e.flags & ~_lib.FLAG_OUT_OVERFLOW):
+                    kwargs["capacity"] = r.capacity * 4
+                else:
+                    raise
 
     # ---------------------------------------------------------------- host-buffer entry point
     def _host_state(self, shapes, chunk, capacity):

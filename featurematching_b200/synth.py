@@ -96,3 +96,63 @@ def hot_path_params(Cc=256, Cf=64, WW=49, seed=99, device="cpu", dtype=torch.flo
         "mix_w1": uniform((WW,), WW), "mix_b1": uniform((1,), WW),
     }
     return {k: v.to(device=device, dtype=dtype) for k, v in p.items()}
+
+
+def seeded_state_dict(module, seed):
+    """A deterministic, portable stand-in for a checkpoint (none ships with the reference, demo/demo.py:99):
+    every floating-point entry of `module.state_dict()` is redrawn from numpy's RandomState in sorted key
+    order with the DISTRIBUTIONS of the reference's own initialisation, so the reference `net` (build
+    container) and featurematching_b200.matcher.Matcher (GPU box) get bit-identical weights without a
+    48 MB file:
+      nn.Linear / nn.Conv2d defaults   U(-1/sqrt(fan_in), 1/sqrt(fan_in)) for weight and bias
+      coarse.* / fine.* matrices       xavier-uniform (network/module/transformer.py:73-76)
+      fine_preprocess.* matrices       kaiming-normal, fan_out (network/module/fine_preprocess.py:27-30)
+      LayerNorm                        weight 1, bias 0;  relative-position tables N(0, 0.02^2)
+    Integer buffers are kept."""
+    import numpy as np
+    rs = np.random.RandomState(seed)
+    out = {}
+    sd = module.state_dict()
+    for k in sorted(sd):
+        v = sd[k]
+        if not v.is_floating_point():
+            out[k] = v.clone()
+            continue
+        shape = tuple(v.shape)
+        parent = k.rsplit(".", 1)[0]
+        is_norm = v.dim() == 1 and any("norm" in part for part in parent.split(".")[-2:])   # norm1, norm_down.0, upsample.norm
+        if is_norm:
+            t = np.ones(shape) if k.endswith(".weight") else np.zeros(shape)
+        elif k.endswith("relative_position_bias_table"):
+            t = 0.02 * rs.standard_normal(shape)
+        elif v.dim() >= 2:
+            fan_out, fan_in = shape[0] * int(np.prod(shape[2:])), int(np.prod(shape[1:]))
+            if k.startswith(("coarse.", "fine.")):
+                b = (6.0 / (fan_in + fan_out)) ** .5
+                t = rs.uniform(-b, b, shape)
+            elif k.startswith("fine_preprocess."):
+                t = rs.standard_normal(shape) * (2.0 / fan_out) ** .5
+            else:
+                b = 1.0 / fan_in ** .5
+                t = rs.uniform(-b, b, shape)
+        else:   # a bias: bound from the sibling weight's fan-in
+            w = sd.get(parent + ".weight")
+            fan_in = int(np.prod(w.shape[1:])) if w is not None and w.dim() >= 2 else shape[0]
+            b = 1.0 / fan_in ** .5
+            t = rs.uniform(-b, b, shape)
+        out[k] = torch.from_numpy(np.asarray(t, dtype=np.float32)).to(v.dtype)
+    return out
+
+
+def images(B, H, W, seed, identical=False, channels=3):
+    """Synthetic image pair [B, channels, H, W] fp32 uniform in [0, 1) (SURVEY.md 8(d): torch.rand images;
+    the datasets feed /255 floats, datasets/scared_new2.py:229-232), numpy-seeded so both machines see
+    the same bits.  identical: image1 = image0 (SURVEY.md 8(d) config (1) variant)."""
+    import numpy as np
+    rs = np.random.RandomState(seed)
+
+    def one():
+        return torch.from_numpy(rs.rand(B, channels, H, W).astype(np.float32))
+
+    a = one()
+    return a, (a.clone() if identical else one())

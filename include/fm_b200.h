@@ -68,10 +68,15 @@ extern "C" {
 #define FM_ST_MAX_CAND 2  /* largest per-unit candidate count seen (sizing hint)    */
 #define FM_ST_LOST 3      /* tokens whose soft-max sums left fp32 range             */
 #define FM_ST_CAND_TOTAL 4
+#define FM_ST_REDO 5      /* 1 = the exact (second) candidate-extraction pass ran           */
 
-#define FM_FLAG_CAND_OVERFLOW 1 /* candidate buffer too small: retry with larger cand_per_row */
+#define FM_FLAG_CAND_OVERFLOW 1 /* candidate buffer too small even for the exact extraction pass
+                                   (entries whose row soft-max exceeds 0.9 thr): retry with a
+                                   larger cand_per_row                                        */
 #define FM_FLAG_OUT_OVERFLOW 2  /* more matches than `capacity`                               */
-#define FM_FLAG_TIE_OVERFLOW 4  /* more than 4 exactly tied matches in one row                */
+#define FM_FLAG_TIE_OVERFLOW 4  /* exactly tied matches beyond 4 per row exceed the shared list
+                                   of 16384 entries (duplicate descriptors en masse); up to
+                                   that, all ties are emitted like the reference's == test    */
 #define FM_FLAG_RANGE 8         /* FM_ST_LOST > 0: scores span > 157 nats below their bound   */
 
 FM_API int fm_version(void);
@@ -83,7 +88,12 @@ FM_API int fm_device_sm_count(void);
 /* ---------------------------------------------------------------- coarse stage
  * Bytes of workspace fm_coarse_match needs.  `cand_per_row` sizes the candidate buffers
  * (records per image-0 token per 256-column block; 4 is ample for thr >= 0.1, the Python shim
- * grows it when FM_FLAG_CAND_OVERFLOW comes back).  Returns 0 on invalid arguments. */
+ * grows it when FM_FLAG_CAND_OVERFLOW comes back).  Returns 0 on invalid arguments.
+ * Candidate extraction is single-pass (a chunk is kept when its best entry exceeds 0.9 thr of the
+ * row's 128-column partial soft-max sum).  When that weak test overflows the buffers -- diffuse rows:
+ * random-init networks, thr << 1/128 -- the call re-runs the statistics kernel ON ITS OWN (decided on
+ * the device, no host round trip; FM_ST_REDO reports it) with the full-row sums as the reference,
+ * which keeps only entries whose row soft-max really exceeds 0.9 thr. */
 FM_API size_t fm_coarse_workspace_bytes(int B, int N0, int N1, int C, int feat_dtype, int cand_per_row);
 
 /* Dual-softmax mutual-nearest-neighbour coarse matching of B frame pairs.

@@ -205,6 +205,81 @@ def fine_chain_with_transformer(ref, name):
     print(f"{name}: mkpts0_f[0]={data['mkpts0_f'][0].tolist()}")
 
 
+FULL_NET = dict(weight_seed=2027, image_seed=7, H=512, W=640, low_thr=0.005)   # weight_seed: M = 39 at low_thr
+
+
+def describe(data):
+    """'key:dtype:shape' of every entry net.forward leaves in `data` (demo/demo.py:108), sorted."""
+    out = []
+    for k in sorted(data):
+        v = data[k]
+        if torch.is_tensor(v):
+            out.append(f"{k}:{str(v.dtype).replace('torch.', '')}:{'x'.join(map(str, v.shape))}")
+        elif isinstance(v, (tuple, torch.Size)):
+            out.append(f"{k}:size:{'x'.join(map(str, v))}")
+        else:
+            out.append(f"{k}:{type(v).__name__}:{v}")
+    return out
+
+
+def run_reference_net(thr, identical, threads=None):
+    """BASELINE configs[0]: ONE 640x512 pair through the UNMODIFIED reference `net` exactly as
+    demo/demo.py:101-108 drives it (net(config=net_configs), load_state_dict, eval, matcher(data)), on
+    CPU.  The checkpoint is synth.seeded_state_dict (none ships); returns (data, seconds of the forward)."""
+    import copy
+    import time
+    net, cfg = reference_shims.load_reference_net()
+    cfg = copy.deepcopy(cfg)
+    cfg["match_coarse"]["thr"] = thr
+    c = FULL_NET
+    if threads:
+        torch.set_num_threads(threads)
+    matcher = net(config=cfg)
+    matcher.load_state_dict(synth.seeded_state_dict(matcher, c["weight_seed"]))
+    matcher = matcher.eval()
+    im0, im1 = synth.images(1, c["H"], c["W"], c["image_seed"], identical=identical)
+    data = {"image0": im0, "image1": im1}
+    with torch.no_grad():
+        t0 = time.perf_counter()
+        matcher(data)
+        el = time.perf_counter() - t0
+    return data, el
+
+
+def full_net_cases():
+    """(1) thr 0.2, two different random images -> M = 0: the keys / dtypes / shapes of `data`;
+    (2) thr 0.005, image1 = image0 -> M = 39: ids, confidences, coordinates, and for each match its
+    margin (conf over thr and over the runner-up of its row and column) so that a bf16 / GPU run
+    can tell robust matches from rounding-decided ones.  A strided sample of the coarse tokens and of
+    the fine map pins the backbone + coarse transformer numerics."""
+    c = FULL_NET
+    d0, _ = run_reference_net(0.2, identical=False)
+    assert d0["b_ids"].numel() == 0
+    d1, _ = run_reference_net(c["low_thr"], identical=True)
+    conf = d1["conf_matrix"][0]
+    i, j = d1["i_ids"], d1["j_ids"]
+    mc = conf[i, j]
+    row = conf[i].clone(); row[torch.arange(len(i)), j] = 0
+    col = conf[:, j].t().clone(); col[torch.arange(len(j)), i] = 0
+    margin = torch.minimum(mc / c["low_thr"], torch.minimum(mc / row.amax(1), mc / col.amax(1)))
+    # every entry a slightly different rounding could turn into a match: conf > 0.7 thr
+    near = torch.nonzero(conf > 0.7 * c["low_thr"])
+    np.savez_compressed(
+        os.path.join(GOLDEN_DIR, "full_net.npz"),
+        keys_m0=np.array(describe({k: v for k, v in d0.items() if k != "conf_matrix"})),
+        keys_low=np.array(describe({k: v for k, v in d1.items() if k != "conf_matrix"})),
+        weight_seed=c["weight_seed"], image_seed=c["image_seed"], H=c["H"], W=c["W"], low_thr=c["low_thr"],
+        b_ids=d1["b_ids"].numpy(), i_ids=i.numpy(), j_ids=j.numpy(), mconf=d1["mconf"].numpy(),
+        mkpts0_c=d1["mkpts0_c"].numpy(), mkpts1_c=d1["mkpts1_c"].numpy(),
+        mkpts0_f=d1["mkpts0_f"].numpy(), mkpts1_f=d1["mkpts1_f"].numpy(),
+        margin=margin.numpy(), near=near.numpy(), near_conf=conf[near[:, 0], near[:, 1]].numpy(),
+        feat_c0_sample=d1["feat_c0"][0, ::97].numpy(), feat_c1_sample=d1["feat_c1"][0, ::97].numpy(),
+        feat_f0_sample=d1["feat_f0"][0, :, ::37, ::41].numpy(),
+    )
+    print(f"full_net: M(thr 0.2)=0, M(thr {c['low_thr']}, identical)={len(i)}, margins {margin.min():.3f}..{margin.max():.3f}, "
+          f"{len(near)} entries above 0.7 thr")
+
+
 def main():
     os.makedirs(GOLDEN_DIR, exist_ok=True)
     ref = reference_shims.load_reference()
@@ -222,6 +297,7 @@ def main():
     transformer_case(ref, "fine_transformer_csc", 5, ("cross", "self", "cross"), 42)
     fine_chain_with_transformer(ref, "fine_chain_tf")
     coarse_transformer_case(ref, "coarse_transformer")
+    full_net_cases()
 
 
 if __name__ == "__main__":

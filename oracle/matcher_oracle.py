@@ -79,6 +79,86 @@ def coarse_match(feat_c0, feat_c1, hw0_i, hw0_c, hw1_c, thr=0.2, border_rm=2,
     return out
 
 
+def coarse_match_chunked(feat_c0, feat_c1, hw0_i, hw0_c, hw1_c, thr=0.2, border_rm=2, temperature=0.1,
+                         dtype=torch.float32, rows=2048):
+    """coarse_match for ONE pair whose N0 x N1 matrix does not fit in memory (1280x1024: 20 480 tokens,
+    1.68 GB per fp32 matrix and the reference makes ~6 of them): the same arithmetic, streamed over
+    blocks of `rows` image-0 tokens.  A dual-softmax row needs only the two log-sum-exp vectors:
+      pass 1  sim block -> row LSE (complete), column LSE (running logaddexp)      coarse_matching_new.py:68
+      pass 2  conf = exp(sim - lse_row) * exp(sim - lse_col); row maxima (complete), running column maxima
+      pass 3  mask = conf > thr & interior & == row max & == column max            coarse_matching_new.py:99-106
+    Returns the dict of coarse_match plus 'lse_row' / 'lse_col' (for the fp64 tie analysis of
+    `chunked_ambiguous`)."""
+    assert feat_c0.shape[0] == 1, "one pair at a time"
+    C = feat_c0.shape[-1]
+    f0 = feat_c0[0].to(dtype) / C ** .5
+    f1 = feat_c1[0].to(dtype) / C ** .5
+    N0, N1 = f0.shape[0], f1.shape[0]
+    h0c, w0c = int(hw0_c[0]), int(hw0_c[1])
+    h1c, w1c = int(hw1_c[0]), int(hw1_c[1])
+    lse_r = torch.empty(N0, dtype=dtype)
+    lse_c = torch.full((N1,), -float("inf"), dtype=dtype)
+    blocks = [(a, min(a + rows, N0)) for a in range(0, N0, rows)]
+    for a, b in blocks:
+        sim = f0[a:b] @ f1.t() / temperature
+        lse_r[a:b] = torch.logsumexp(sim, 1)
+        lse_c = torch.logaddexp(lse_c, torch.logsumexp(sim, 0))
+
+    def conf_block(a, b):
+        sim = f0[a:b] @ f1.t() / temperature
+        return torch.exp(sim - lse_r[a:b, None]) * torch.exp(sim - lse_c[None, :])
+
+    rmax = torch.empty(N0, dtype=dtype)
+    cmax = torch.zeros(N1, dtype=dtype)
+    for a, b in blocks:
+        conf = conf_block(a, b)
+        rmax[a:b] = conf.amax(1)
+        cmax = torch.maximum(cmax, conf.amax(0))
+    in0 = interior_mask(h0c, w0c, border_rm)
+    in1 = interior_mask(h1c, w1c, border_rm)
+    ii, jj, cc = [], [], []
+    for a, b in blocks:
+        conf = conf_block(a, b)
+        mask = (conf > thr) & in0[a:b, None] & in1[None, :] & (conf == rmax[a:b, None]) & (conf == cmax[None, :])
+        i, j = torch.nonzero(mask, as_tuple=True)
+        ii.append(i + a); jj.append(j); cc.append(conf[i, j])
+    i_ids, j_ids, mconf = torch.cat(ii), torch.cat(jj), torch.cat(cc)
+    b_ids = torch.zeros_like(i_ids)
+    scale = hw0_i[0] / h0c
+    return {
+        "b_ids": b_ids, "i_ids": i_ids, "j_ids": j_ids, "m_bids": b_ids, "gt_mask": mconf == 0,
+        "mconf": mconf[mconf != 0],
+        "mkpts0_c": torch.stack([i_ids % w0c, torch.div(i_ids, w0c, rounding_mode="floor")], 1) * scale,
+        "mkpts1_c": torch.stack([j_ids % w1c, torch.div(j_ids, w1c, rounding_mode="floor")], 1) * scale,
+        "lse_row": lse_r, "lse_col": lse_c,
+    }
+
+
+def chunked_ambiguous(feat_c0, feat_c1, i, j, thr, temperature, eps):
+    """Tie rule of oracle/compare.py for an entry (i, j) of a pair too large for a dense fp64 matrix: is
+    conf_ij, in fp64, within `eps` (relative) of thr or of the best rival of its row or column?  Needs the
+    fp64 LSE vectors, which cost one streamed pass each time -- only called for entries that differ."""
+    C = feat_c0.shape[-1]
+    f0 = feat_c0[0].double() / C ** .5
+    f1 = feat_c1[0].double() / C ** .5
+    lse_c = torch.full((f1.shape[0],), -float("inf"), dtype=torch.float64)
+    lse_r = torch.empty(f0.shape[0], dtype=torch.float64)
+    for a in range(0, f0.shape[0], 1024):
+        sim = f0[a:a + 1024] @ f1.t() / temperature
+        lse_r[a:a + 1024] = torch.logsumexp(sim, 1)
+        lse_c = torch.logaddexp(lse_c, torch.logsumexp(sim, 0))
+    row = f0[i] @ f1.t() / temperature
+    col = f0 @ f1[j] / temperature
+    crow = torch.exp(row - lse_r[i]) * torch.exp(row - lse_c)
+    ccol = torch.exp(col - lse_r) * torch.exp(col - lse_c[j])
+    c = crow[j].item()
+    crow[j] = -1
+    ccol[i] = -1
+    scale = max(c, thr)
+    return (abs(c - thr) <= eps * scale or abs(c - crow.max().item()) <= eps * scale
+            or abs(c - ccol.max().item()) <= eps * scale)
+
+
 # --------------------------------------------------------------------------- fine: windows
 def gather_windows(feat_f, b_ids, cell_ids, w_c, W=7, stride=4, pad=2, dtype=torch.float32):
     """Windows of `F.unfold(feat_f, (W, W), stride, padding=pad)` at (b, cell) -> [M, W*W, C].

@@ -10,6 +10,14 @@ restated here from kornia's published semantics (the reference pins no version):
   kornia.geometry.subpix.dsnt.spatial_expectation2d(inp[B, N, H, W], True)
       -> [B, N, 2] = cat[sum(x * p), sum(y * p)]
 
+The full matcher (`network/net.py`) additionally imports `timm.models.layers.{DropPath, to_2tuple,
+trunc_normal_}` (swin...py:15, pose_pred.py:13) and `yacs.config.CfgNode` (demo/net_config.py:1); both are
+absent and un-pinned, and are shimmed from their published semantics (`_install_net_shims`):
+  DropPath(p)         identity in eval mode (stochastic depth only acts in training)
+  to_2tuple(x)        (x, x) unless x is already an iterable
+  trunc_normal_       torch.nn.init.trunc_normal_ (same signature)
+  CfgNode             attribute-access dict (only `CN()`, attribute assignment and `.items()` are used)
+
 `/root/reference` does not exist on the GPU box; `available()` says whether the
 real reference can be used.
 """
@@ -79,7 +87,77 @@ def _install_shims():
     })
 
 
+def _install_net_shims():
+    """timm.models.layers + yacs.config for network/net.py and demo/net_config.py."""
+    try:
+        import timm.models.layers  # noqa: F401
+    except Exception:
+        import collections.abc
+
+        class DropPath(torch.nn.Module):
+            def __init__(self, drop_prob=0.0, scale_by_keep=True):
+                super().__init__()
+                self.drop_prob = drop_prob
+
+            def forward(self, x):
+                if self.drop_prob == 0.0 or not self.training:
+                    return x
+                raise NotImplementedError("DropPath shim: training mode is not needed by the oracle")
+
+        def to_2tuple(x):
+            if isinstance(x, collections.abc.Iterable) and not isinstance(x, str):
+                return tuple(x)
+            return (x, x)
+
+        timm = types.ModuleType("timm")
+        models = types.ModuleType("timm.models")
+        layers = types.ModuleType("timm.models.layers")
+        layers.DropPath, layers.to_2tuple, layers.trunc_normal_ = DropPath, to_2tuple, torch.nn.init.trunc_normal_
+        models.layers = layers
+        timm.models = models
+        sys.modules.update({"timm": timm, "timm.models": models, "timm.models.layers": layers})
+    try:
+        import yacs.config  # noqa: F401
+    except Exception:
+        class CfgNode(dict):
+            def __getattr__(self, k):
+                try:
+                    return self[k]
+                except KeyError as e:
+                    raise AttributeError(k) from e
+
+            def __setattr__(self, k, v):
+                self[k] = v
+
+        yacs = types.ModuleType("yacs")
+        config = types.ModuleType("yacs.config")
+        config.CfgNode = CfgNode
+        yacs.config = config
+        sys.modules.update({"yacs": yacs, "yacs.config": config})
+
+
 _CACHE = {}
+
+
+def load_reference_net():
+    """Returns (net class, net_configs dict) of the UNMODIFIED reference: network/net.py:20 and the
+    demo configuration demo/net_config.py:48 (what demo/demo.py:105 builds)."""
+    if "net" in _CACHE:
+        return _CACHE["net"]
+    if not available():
+        raise RuntimeError(f"reference not present at {REFERENCE_ROOT}")
+    _install_shims()
+    _install_net_shims()
+    if REFERENCE_ROOT not in sys.path:
+        sys.path.insert(0, REFERENCE_ROOT)
+    import importlib.util
+    from network.net import net
+    spec = importlib.util.spec_from_file_location("fm_ref_demo_net_config",
+                                                  os.path.join(REFERENCE_ROOT, "demo", "net_config.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    _CACHE["net"] = (net, mod.net_configs)
+    return _CACHE["net"]
 
 
 def load_reference():
@@ -117,4 +195,5 @@ def default_config():
         "fine": {"d_model": 64, "nhead": 8, "layer_names": ["self", "cross"],
                  "attention": "linear"},
         "pose_net_flag": "none",
+        "backbone_type": "swin", "input_channel": 3, "resolution": (8, 2),
     }
