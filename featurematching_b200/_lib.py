@@ -25,6 +25,7 @@ SIGNATURES = {
     "fm_version": (_I, []),
     "fm_last_error_string": (_c.c_char_p, []),
     "fm_device_sm_count": (_I, []),
+    "fm_launch_count": (_c.c_longlong, []),
     "fm_coarse_workspace_bytes": (_Z, [_I] * 6),
     "fm_coarse_match": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _F, _F, _I, _F, _P, _P,
                              _P, _P, _P, _P, _P, _P, _P, _I, _P, _Z, _I, _P]),

@@ -82,6 +82,7 @@ cudaError_t launch_coarse_prep(const void* f0, const void* f1, int dtype, const 
     else
         coarse_prep_kernel<false><<<grid, 256, 0, st>>>(f0, f1, nullptr, nullptr, w.norm0, w.maxnorm,
                                                          d.N0, d.N1, d.N0pad, d.C);
+    count_launch();
     return cudaGetLastError();
 }
 

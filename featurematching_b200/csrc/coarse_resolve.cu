@@ -301,7 +301,7 @@ cudaError_t launch_coarse_finish_lse(const CoarseResolveParams& p, const CoarseW
     const int nmax = d.N0 > d.N1 ? d.N0 : d.N1;
     finish_lse_kernel<<<dim3((nmax + 255) / 256, d.B), 256, 0, st>>>(d, p.a2, w.norm0, w.maxnorm, w.rowpart,
                                                                      w.colpart, w.l2row, w.l2col, p.status,
-                                                                     with_gate ? w.redo : nullptr);
+                                                                     with_gate ? w.redo : nullptr); count_launch();
     return cudaGetLastError();
 }
 
@@ -309,16 +309,16 @@ cudaError_t launch_coarse_resolve(const CoarseResolveParams& p, const CoarseWork
     const CoarseDims& d = p.d;
     const unsigned cgrid = static_cast<unsigned>(d.num_pools) * kCandBlocksPerPool;
     cand_best_kernel<<<cgrid, kCandWarps * 32, 0, st>>>(d, p.a2, p.thr, w.hot_meta, w.hot_dots, w.hot_count, w.l2row,
-                                                        w.l2col, w.rowbest, w.colbest, p.status);
+                                                        w.l2col, w.rowbest, w.colbest, p.status); count_launch();
     cand_select_kernel<<<cgrid, kCandWarps * 32, 0, st>>>(d, p.a2, p.thr, p.h0c, p.w0c, p.h1c, p.w1c, p.border,
                                                           w.hot_meta, w.hot_dots, w.hot_count, w.l2row, w.l2col,
                                                           w.rowbest, w.colbest, w.rowcnt, w.rowslot, w.tie_count, w.tie_list,
-                                                          p.status);
+                                                          p.status); count_launch();
     const int nrows = d.B * d.N0;
     const int nblocks = (nrows + kScanBlock - 1) / kScanBlock;
-    row_blocksum_kernel<<<nblocks, kScanBlock, 0, st>>>(w.rowcnt, nrows, w.tie_count, w.blocksum);
-    blocksum_scan_kernel<<<1, kScanBlock, 0, st>>>(w.blocksum, nblocks, p.capacity, p.status);
-    emit_kernel<<<nblocks, kScanBlock, 0, st>>>(p, w.rowcnt, w.rowslot, w.tie_count, w.tie_list, w.blocksum);
+    row_blocksum_kernel<<<nblocks, kScanBlock, 0, st>>>(w.rowcnt, nrows, w.tie_count, w.blocksum); count_launch();
+    blocksum_scan_kernel<<<1, kScanBlock, 0, st>>>(w.blocksum, nblocks, p.capacity, p.status); count_launch();
+    emit_kernel<<<nblocks, kScanBlock, 0, st>>>(p, w.rowcnt, w.rowslot, w.tie_count, w.tie_list, w.blocksum); count_launch();
     return cudaGetLastError();
 }
 

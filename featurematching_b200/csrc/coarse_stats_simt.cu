@@ -113,8 +113,8 @@ cudaError_t launch_coarse_stats_simt(const __nv_bfloat16* f0, const __nv_bfloat1
     e = cudaMemsetAsync(p.colpart, 0, sizeof(float) * d.B * d.S * d.N1pad, st);
     if (e != cudaSuccess) return e;
     dim3 grid((d.N1 + kT - 1) / kT, (d.N0 + kT - 1) / kT, d.B);
-    coarse_stats_simt_kernel<0><<<grid, 256, smem, st>>>(f0, f1, p);
-    coarse_stats_simt_kernel<1><<<grid, 256, smem, st>>>(f0, f1, p);
+    coarse_stats_simt_kernel<0><<<grid, 256, smem, st>>>(f0, f1, p); count_launch();
+    coarse_stats_simt_kernel<1><<<grid, 256, smem, st>>>(f0, f1, p); count_launch();
     return cudaGetLastError();
 }
 

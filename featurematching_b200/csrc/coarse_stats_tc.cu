@@ -409,6 +409,7 @@ cudaError_t launch_coarse_stats_tc(const __nv_bfloat16* f0, const __nv_bfloat16*
     const int grid = p.d.num_pools;   // one record pool per CTA
     if (p.l2row) coarse_stats_tc_kernel<true><<<grid, kCoarseThreads, kSmemBytes, st>>>(tm0, tm1, p);
     else coarse_stats_tc_kernel<false><<<grid, kCoarseThreads, kSmemBytes, st>>>(tm0, tm1, p);
+    count_launch();
     return cudaGetLastError();
 }
 

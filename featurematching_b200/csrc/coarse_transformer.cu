@@ -589,7 +589,7 @@ cudaError_t launch_gemm(const CUtensorMap& a0, const CUtensorMap& a1, const CUte
     p.num_units = p.B * p.tiles_per_img * p.n_tiles;
     if (p.num_units == 0) return cudaSuccess;
     const int grid = 2 * std::min(num_sms / 2, p.num_units);   // whole CTA pairs
-    ct_gemm_kernel<kEpi><<<grid, kGemmThreads, kGemmSmem, st>>>(a0, a1, w, p);
+    ct_gemm_kernel<kEpi><<<grid, kGemmThreads, kGemmSmem, st>>>(a0, a1, w, p); count_launch();
     return cudaGetLastError();
 }
 
@@ -634,7 +634,7 @@ cudaError_t launch_coarse_transformer(const float* feat0, const float* feat1, in
         lp.mlp0 = static_cast<const float*>(src[4]); lp.mlp2 = static_cast<const float*>(src[5]);
         lp.n1w = static_cast<const float*>(src[6]); lp.n1b = static_cast<const float*>(src[7]);
         lp.n2w = static_cast<const float*>(src[8]); lp.n2b = static_cast<const float*>(src[9]);
-        ct_pack_kernel<<<296, 256, 0, st>>>(lp, ws + pl.blobs + static_cast<size_t>(l) * kLayerBlobBytes);
+        ct_pack_kernel<<<296, 256, 0, st>>>(lp, ws + pl.blobs + static_cast<size_t>(l) * kLayerBlobBytes); count_launch();
     }
     if ((e = cudaMemsetAsync(kvbd, 0, static_cast<size_t>(B) * 2 * kD * kD * 2, st)) != cudaSuccess) return e;
     for (int s = 0; s < 2; ++s) {
@@ -643,7 +643,7 @@ cudaError_t launch_coarse_transformer(const float* feat0, const float* feat1, in
         const int grid = static_cast<int>(std::min<size_t>((n4 + 255) / 256, static_cast<size_t>(num_sms) * 16));
         ct_split_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(ins[s]), reinterpret_cast<float4*>(xs[s]),
                                               reinterpret_cast<uint2*>(xp[s]),
-                                              reinterpret_cast<uint2*>(xp[s] + static_cast<size_t>(B) * Ls[s] * kD), n4);
+                                              reinterpret_cast<uint2*>(xp[s] + static_cast<size_t>(B) * Ls[s] * kD), n4); count_launch();
     }
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
 
@@ -696,8 +696,8 @@ cudaError_t launch_coarse_transformer(const float* feat0, const float* feat1, in
             }
             const int chunk_tokens = (S + chunks - 1) / chunks;
             chunks = (S + chunk_tokens - 1) / chunk_tokens;
-            ct_kv_partial_kernel<<<dim3(chunks, B), 256, kKvSmem, st>>>(kf, vf, S, chunk_tokens, kvpart, kspart);
-            ct_kv_finalize_kernel<<<dim3(kH, B), 256, 0, st>>>(kvpart, kspart, chunks, kvbd, ksum);
+            ct_kv_partial_kernel<<<dim3(chunks, B), 256, kKvSmem, st>>>(kf, vf, S, chunk_tokens, kvpart, kspart); count_launch();
+            ct_kv_finalize_kernel<<<dim3(kH, B), 256, 0, st>>>(kvpart, kspart, chunks, kvbd, ksum); count_launch();
             // 3. Q', Z
             p.L = Lx; p.planes = qp; p.plane_stride = Rx * kD; p.ld = kD; p.ksum = ksum; p.z = z;
             if ((e = launch_gemm<kEpiQ>(m_x[xs_], m_x[xs_], w_q, p, kD, kD, num_sms, st)) != cudaSuccess) return e;

@@ -223,7 +223,7 @@ cudaError_t launch_gather_t(const GatherParams& p, bool merge, int num_sms, cuda
     int grid = num_sms * (per_sm > 0 ? per_sm : 1);
     if (grid > 2 * p.capacity) grid = 2 * p.capacity;
     if (grid < 1) grid = 1;
-    kern<<<grid, kThreads, smem, st>>>(p);
+    kern<<<grid, kThreads, smem, st>>>(p); count_launch();
     return cudaGetLastError();
 }
 
@@ -261,6 +261,7 @@ cudaError_t launch_to_nhwc(const void* src, int src_dtype, int B, int C, int H, 
     else
         to_nhwc_kernel<__nv_bfloat16><<<grid, 256, smem, st>>>(static_cast<const __nv_bfloat16*>(src),
                                                                static_cast<__nv_bfloat16*>(dst), C, H, W);
+    count_launch();
     return cudaGetLastError();
 }
 

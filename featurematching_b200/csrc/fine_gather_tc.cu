@@ -448,7 +448,7 @@ cudaError_t launch_window_merge(const CUtensorMap& tf0, const CUtensorMap& tf1, 
     cudaError_t e = cudaFuncSetAttribute(window_merge_kernel<TO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
     if (e != cudaSuccess) return e;
-    window_merge_kernel<TO><<<grid, kGThreads, smem, st>>>(tf0, tf1, tw, to0, to1, wp);
+    window_merge_kernel<TO><<<grid, kGThreads, smem, st>>>(tf0, tf1, tw, to0, to1, wp); count_launch();
     return cudaGetLastError();
 }
 
@@ -475,14 +475,14 @@ cudaError_t launch_fine_gather_tc(const void* ff0, const void* ff1, const void* 
         return cudaErrorInvalidValue;
     }
     // ---- 1. fold the weights; bf16 tokens
-    fold_kernel<<<kCf, Cc < kCf ? kCf : Cc, 0, st>>>(down_w, down_b, merge_w, merge_b, Cc, ws.wa_split, ws.wc_split, ws.bc);
+    fold_kernel<<<kCf, Cc < kCf ? kCf : Cc, 0, st>>>(down_w, down_b, merge_w, merge_b, Cc, ws.wa_split, ws.wc_split, ws.bc); count_launch();
     const __nv_bfloat16* tok[2] = {static_cast<const __nv_bfloat16*>(fc0), static_cast<const __nv_bfloat16*>(fc1)};
     if (f32_tok) {
         const size_t n8[2] = {static_cast<size_t>(B) * N0 * Cc / 8, static_cast<size_t>(B) * N1 * Cc / 8};
         const void* src[2] = {fc0, fc1};
         for (int s = 0; s < 2; ++s) {
             const int grid = static_cast<int>(std::min<size_t>((n8[s] + 255) / 256, static_cast<size_t>(num_sms) * 8));
-            cast_bf16_kernel<<<grid, 256, 0, st>>>(static_cast<const float*>(src[s]), ws.tok[s], n8[s]);
+            cast_bf16_kernel<<<grid, 256, 0, st>>>(static_cast<const float*>(src[s]), ws.tok[s], n8[s]); count_launch();
             tok[s] = ws.tok[s];
         }
     }
@@ -534,7 +534,7 @@ cudaError_t launch_fine_gather_tc(const void* ff0, const void* ff1, const void* 
     const size_t smem_ctx = static_cast<size_t>(cp.KC) * kSplit * kWsplitBytes + kGStages * kStageBytes + sizeof(GemmCtl) + 1024;
     cudaError_t e = cudaFuncSetAttribute(ctx_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_ctx));
     if (e != cudaSuccess) return e;
-    ctx_gemm_kernel<<<cp.tiles < num_sms ? cp.tiles : num_sms, kGThreads, smem_ctx, st>>>(t_tok[0], t_tok[1], t_wc, cp);
+    ctx_gemm_kernel<<<cp.tiles < num_sms ? cp.tiles : num_sms, kGThreads, smem_ctx, st>>>(t_tok[0], t_tok[1], t_wc, cp); count_launch();
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     // ---- 3. windows

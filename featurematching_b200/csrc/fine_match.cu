@@ -258,7 +258,7 @@ cudaError_t launch(const void* win0, const void* win1, const float* mk0, const f
     if (grid > need) grid = need;
     if (grid < 1) grid = 1;
     kern<<<grid, kWarps * 32, smem, st>>>(static_cast<const T*>(win0), static_cast<const T*>(win1), mk0, mk1, w0, b0,
-                                         w1, b1, count, capacity, WW, W, scale, out0, out1);
+                                         w1, b1, count, capacity, WW, W, scale, out0, out1); count_launch();
     return cudaGetLastError();
 }
 
@@ -317,7 +317,7 @@ cudaError_t launch_pack_matches(const int64_t* b_ids, const int64_t* i_ids, cons
     if (grid < 1) grid = 1;
     pack_matches_kernel<<<grid, 256, 0, st>>>(b_ids, i_ids, j_ids, mconf, mk0, mk1, count, capacity, pair_offset,
                                               static_cast<MatchRecord*>(records), chunk_counts, chunk_index,
-                                              total_capacity);
+                                              total_capacity); count_launch();
     return cudaGetLastError();
 }
 

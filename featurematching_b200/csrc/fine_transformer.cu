@@ -512,7 +512,7 @@ cudaError_t launch_fine_transformer(const float* win0, const float* win1, const 
     for (int l = 0; l < n_layers; ++l) {
         const float* const* q = layer_ptrs + 10 * l;
         TfLayerParams lp{q[0], q[1], q[2], q[3], q[4], q[5], q[6], q[7], q[8], q[9]};
-        tf_pack_kernel<<<20, 256, 0, st>>>(lp, blobs + static_cast<size_t>(l) * kBlobBytes);
+        tf_pack_kernel<<<20, 256, 0, st>>>(lp, blobs + static_cast<size_t>(l) * kBlobBytes); count_launch();
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
@@ -531,7 +531,7 @@ cudaError_t launch_fine_transformer(const float* win0, const float* win1, const 
         p.out[0] = out0; p.out[1] = out1;
         p.count = count; p.capacity = capacity; p.WW = WW;
         p.blob = blobs + static_cast<size_t>(l) * kBlobBytes;
-        kern[kinds[l] ? 1 : 0]<<<grid, kTfThreads, kTfSmem, st>>>(p);
+        kern[kinds[l] ? 1 : 0]<<<grid, kTfThreads, kTfSmem, st>>>(p); count_launch();
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }

@@ -3,6 +3,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <atomic>
 #include <mutex>
 #include <vector>
 
@@ -18,6 +19,9 @@ void set_error(const char* fmt, ...) {
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
 }
+
+static std::atomic<long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 static int cuda_fail(cudaError_t e, const char* what) {
     set_error("%s: %s", what, cudaGetErrorString(e));
@@ -289,6 +293,8 @@ int fm_version(void) { return FM_B200_VERSION; }
 const char* fm_last_error_string(void) { return g_err; }
 
 int fm_device_sm_count(void) { return sm_count(); }
+
+long long fm_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 size_t fm_coarse_workspace_bytes(int B, int N0, int N1, int C, int feat_dtype, int cand_per_row) {
     if (B < 1 || N0 < 1 || N1 < 1 || C < 64 || C > kMaxC || C % 64 || !dtype_ok(feat_dtype) || cand_per_row < 1)

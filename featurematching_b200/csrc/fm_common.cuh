@@ -129,6 +129,10 @@ cudaError_t launch_coarse_resolve(const CoarseResolveParams& p, const CoarseWork
 
 void set_error(const char* fmt, ...);
 
+// Kernel launches issued by this library since load (fm_launch_count): every launcher bumps it right after a
+// <<<>>>.  Host-side bookkeeping only; bench.py turns the difference over its timed region into `gpu_launches`.
+void count_launch(int n = 1);
+
 // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) belongs to a device's context: `mask` (one static per
 // kernel) remembers the devices it was set on.  True = the caller must set it for the current device.
 inline bool needs_attr_on_this_device(unsigned long long* mask) {

@@ -243,6 +243,12 @@ class FinePreprocess(nn.Module):
             return win0, win1
         if self.cat_c_feat:
             _require_cuda(feat_c0, feat_c1)
+            # the window-context GEMM reads the tokens in bf16, like the coarse contraction: take the rounding the
+            # B200 coarse transformer already wrote (bit-equal to the cast the kernel would do itself)
+            t0, t1 = getattr(feat_c0, "_fm_bf16", None), getattr(feat_c1, "_fm_bf16", None)
+            if (t0 is not None and t1 is not None and t0.shape == feat_c0.shape and t1.shape == feat_c1.shape
+                    and t0.device == feat_c0.device):
+                feat_c0, feat_c1 = t0, t1
             c0, c1 = _feat(feat_c0), _feat(feat_c1)
             if c0.dtype != c1.dtype:
                 c1 = c1.to(c0.dtype)

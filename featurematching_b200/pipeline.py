@@ -7,8 +7,9 @@ synchronisation (at the caller's choosing) instead of the reference's one per st
 (torch.where at coarse_matching_new.py:109, the shape test at fine_preprocess.py:37).
 
 `gather_matches` is the one cross-GPU step: ranks own disjoint frame pairs; their packed match
-records are exchanged with a single padded all_gather (NCCL over NVLink on GPUs, gloo in the CPU
-tests) -- the analogue of the reference's pickled all_gather (utils/comm.py:141-176).
+records go to the consumer rank with one grouped send / receive (or to every rank with one padded
+all_gather) -- NCCL over NVLink on GPUs, gloo in the CPU tests; the analogue of the reference's pickled
+gather / all_gather (utils/comm.py:141-219).
 """
 import numpy as np
 import torch
@@ -259,59 +260,87 @@ def unpack_records(buf, capacity, world):
     return [a[r, 1:1 + int(a[r, 0]["pair"])] for r in range(world)]
 
 
-def gather_matches(records, capacity, group=None):
-    """All ranks receive every rank's packed records: one padded all_gather, no size exchange and
-    no host synchronisation (the count travels in each rank's header record).  Every rank must
-    call it, also with zero matches.  `records`: uint8 [(capacity + 1) * 40] on the rank's device
-    (CPU tensors with the gloo backend).  Returns uint8 [world * (capacity + 1) * 40]."""
+def gather_matches(records, capacity, group=None, dst=None):
+    """The one cross-GPU step: ranks own disjoint frame pairs and exchange their packed match records.
+
+    dst = None: every rank receives every rank's records (one padded all_gather).
+    dst = r:    only the consumer rank r receives them (dist.gather = grouped ncclSend / ncclRecv: the seven
+                other ranks of a box run a 5.8 MB send instead of an 8 x 5.8 MB all-gather kernel next to
+                their persistent 148-CTA kernels) -- the role of the reference's `gather`, utils/comm.py:179-219;
+                returns None on the other ranks.
+    No size exchange and no host synchronisation either way (the count travels in each rank's header record).
+    Every rank must call it, also with zero matches.  `records`: uint8 [(capacity + 1) * 40] on the rank's
+    device (CPU tensors with the gloo backend).  Returns uint8 [world * (capacity + 1) * 40] or None."""
     import torch.distributed as dist
     world = dist.get_world_size(group)
     n = (capacity + 1) * _lib.RECORD_BYTES
-    out = torch.empty(world * n, dtype=torch.uint8, device=records.device)
-    dist.all_gather_into_tensor(out, records[:n].contiguous(), group=group)
-    return out
+    mine = records[:n].contiguous()
+    if dst is None:
+        out = torch.empty(world * n, dtype=torch.uint8, device=records.device)
+        dist.all_gather_into_tensor(out, mine, group=group)
+        return out
+    if dist.get_rank(group) == dst:
+        out = torch.empty(world * n, dtype=torch.uint8, device=records.device)
+        dist.gather(mine, [out[r * n:(r + 1) * n] for r in range(world)], dst=dst, group=group)
+        return out
+    dist.gather(mine, None, dst=dst, group=group)
+    return None
 
 
 class OverlappedGather:
-    """The match-list all_gather on a side stream, so that step k's exchange overlaps step k + 1's
-    kernels ("gather once per batch, overlap with the next batch's compute").
+    """The match-list exchange on a side stream, placed under the NEXT step's HBM-bound fine kernels rather than
+    under its tensor-core kernel ("gather once per batch, overlap with the next batch's compute"):
 
-        g = OverlappedGather(device)
+        g = OverlappedGather(device, dst=0)        # dst=None: all_gather to every rank
         for batch in batches:
-            r = head.run(..., pack=False)          # everything but the record pack
-            g.before_pack()                        # the records buffer is free again
+            coarse stage of this batch             # the persistent 148-CTA kernel keeps every SM to itself
+            g.launch()                             # exchange of the PREVIOUS batch starts here, behind it
+            gather / fine transformer / fine match
+            g.before_pack()                        # the records buffer is free again (device-side wait)
             pack records into r.records
-            out = g.launch(r.records, r.capacity)  # valid after g.finish() / the next before_pack()
-        g.finish()
+            g.stage(r.records, r.capacity)         # marks them ready; nothing is sent yet
+        out = g.finish()                           # sends the last batch, joins the side stream
 
-    The records buffer is read by the collective while the next step computes; `before_pack`
-    makes the next pack wait for it (an event wait on the device, no host synchronisation)."""
+    No host synchronisation anywhere; `out` (on the consumer rank, None elsewhere when dst is set) is valid once
+    the current stream has passed finish() / the next before_pack()."""
 
-    def __init__(self, device, group=None):
+    def __init__(self, device, group=None, dst=None):
         self.device = torch.device(device)
-        self.group = group
+        self.group, self.dst = group, dst
         self.side = torch.cuda.Stream(device=self.device)
         self.packed = torch.cuda.Event()
+        self.gate = torch.cuda.Event()
         self.done = torch.cuda.Event()
+        self.staged = None
         self.pending = False
         self.out = None
 
-    def before_pack(self):
-        if self.pending:
-            torch.cuda.current_stream(self.device).wait_event(self.done)
+    def stage(self, records, capacity):
+        self.packed.record(torch.cuda.current_stream(self.device))
+        self.staged = (records, capacity)
 
-    def launch(self, records, capacity):
-        cur = torch.cuda.current_stream(self.device)
-        self.packed.record(cur)
+    def launch(self):
+        if self.staged is None:
+            return self.out
+        records, capacity = self.staged
+        self.staged = None
+        self.gate.record(torch.cuda.current_stream(self.device))   # behind whatever the caller enqueued so far
         self.side.wait_event(self.packed)
+        self.side.wait_event(self.gate)
         with torch.cuda.stream(self.side):
-            self.out = gather_matches(records, capacity, self.group)
+            self.out = gather_matches(records, capacity, self.group, self.dst)
             self.done.record(self.side)
         self.pending = True
         return self.out
 
+    def before_pack(self):
+        self.launch()
+        if self.pending:
+            torch.cuda.current_stream(self.device).wait_event(self.done)
+
     def finish(self):
-        """Joins the side stream into the current one (device-side); returns the last result."""
+        """Sends what is staged and joins the side stream into the current one (device-side)."""
+        self.launch()
         if self.pending:
             torch.cuda.current_stream(self.device).wait_event(self.done)
             self.pending = False

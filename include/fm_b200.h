@@ -85,6 +85,10 @@ FM_API const char* fm_last_error_string(void);
 /* Number of SMs of the current device (used for grid sizing); <0 on error. */
 FM_API int fm_device_sm_count(void);
 
+/* Kernel launches this library has issued since it was loaded (all threads, all devices).  Take the
+ * difference around a region to count the library's own launches in it. */
+FM_API long long fm_launch_count(void);
+
 /* ---------------------------------------------------------------- coarse stage
  * Bytes of workspace fm_coarse_match needs.  `cand_per_row` sizes the candidate buffers
  * (records per image-0 token per 256-column block; 4 is ample for thr >= 0.1, the Python shim

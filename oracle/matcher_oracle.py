@@ -28,16 +28,16 @@ def coarse_confidence(feat_c0, feat_c1, temperature, dtype=torch.float32):
     return torch.softmax(sim, 1) * torch.softmax(sim, 2)
 
 
-def interior_mask(h, w, border):
+def interior_mask(h, w, border, device=None):
     """[h*w] bool: cell (r, c) is at least `border` cells from every edge.
 
     network/utils/coarse_matching_new.py:11-28 (mask_border sets False where any of the
     four grid coordinates is < b or >= dim - b); b <= 0 leaves everything True.
     """
     if border <= 0:
-        return torch.ones(h * w, dtype=torch.bool)
-    r = torch.arange(h).unsqueeze(1).expand(h, w)
-    c = torch.arange(w).unsqueeze(0).expand(h, w)
+        return torch.ones(h * w, dtype=torch.bool, device=device)
+    r = torch.arange(h, device=device).unsqueeze(1).expand(h, w)
+    c = torch.arange(w, device=device).unsqueeze(0).expand(h, w)
     ok = (r >= border) & (r < h - border) & (c >= border) & (c < w - border)
     return ok.reshape(-1)
 
@@ -57,8 +57,8 @@ def coarse_match(feat_c0, feat_c1, hw0_i, hw0_c, hw1_c, thr=0.2, border_rm=2,
     h0c, w0c = int(hw0_c[0]), int(hw0_c[1])
     h1c, w1c = int(hw1_c[0]), int(hw1_c[1])
     mask = conf > thr
-    mask &= interior_mask(h0c, w0c, border_rm)[None, :, None]
-    mask &= interior_mask(h1c, w1c, border_rm)[None, None, :]
+    mask &= interior_mask(h0c, w0c, border_rm, conf.device)[None, :, None]
+    mask &= interior_mask(h1c, w1c, border_rm, conf.device)[None, None, :]
     mask &= conf == conf.amax(dim=2, keepdim=True)
     mask &= conf == conf.amax(dim=1, keepdim=True)
     b_ids, i_ids, j_ids = torch.nonzero(mask, as_tuple=True)
@@ -172,8 +172,8 @@ def gather_windows(feat_f, b_ids, cell_ids, w_c, W=7, stride=4, pad=2, dtype=tor
     M = b_ids.shape[0]
     r = torch.div(cell_ids, w_c, rounding_mode="floor")
     c = cell_ids % w_c
-    dy = torch.arange(W).repeat_interleave(W)
-    dx = torch.arange(W).repeat(W)
+    dy = torch.arange(W, device=feat_f.device).repeat_interleave(W)
+    dx = torch.arange(W, device=feat_f.device).repeat(W)
     yy = (stride * r - pad)[:, None] + dy[None, :]          # [M, WW]
     xx = (stride * c - pad)[:, None] + dx[None, :]
     inside = (yy >= 0) & (yy < Hf) & (xx >= 0) & (xx < Wf)
@@ -199,7 +199,7 @@ def fine_preprocess(feat_f0, feat_f1, feat_c0, feat_c1, b_ids, i_ids, j_ids,
     stride = int(hw0_f[0]) // int(hw0_c[0])
     cf = feat_f0.shape[1]
     if b_ids.shape[0] == 0:
-        z = torch.empty(0, W * W, cf, dtype=dtype)
+        z = torch.empty(0, W * W, cf, dtype=dtype, device=feat_f0.device)
         return z, z.clone()
     win0 = gather_windows(feat_f0, b_ids, i_ids, int(hw0_c[1]), W, stride, 2, dtype)
     win1 = gather_windows(feat_f1, b_ids, j_ids, int(hw1_c[1]), W, stride, 2, dtype)
@@ -216,13 +216,13 @@ def fine_preprocess(feat_f0, feat_f1, feat_c0, feat_c1, b_ids, i_ids, j_ids,
 
 
 # --------------------------------------------------------------------------- fine: matching
-def window_grid(W, dtype=torch.float32):
+def window_grid(W, dtype=torch.float32, device=None):
     """[WW, 2] (x, y) normalised window coordinates, row-major (ww = y * W + x).
 
     kornia create_meshgrid(W, W, True) as called at
     network/utils/fine_matching_new.py:66: x_k = (k / (W - 1) - 0.5) * 2.
     """
-    k = torch.linspace(0, W - 1, W, dtype=dtype)
+    k = torch.linspace(0, W - 1, W, dtype=dtype, device=device)
     k = (k / (W - 1) - 0.5) * 2
     gx = k.repeat(W)
     gy = k.repeat_interleave(W)
@@ -265,7 +265,7 @@ def fine_match(win0, win1, mkpts0_c, mkpts1_c, params, hw0_i, hw0_f, dtype=torch
     w1, b1 = params["mix_w1"].to(dtype).reshape(-1), params["mix_b1"].to(dtype).reshape(())
     mixed0 = torch.einsum("r,mrc->mc", w0, f0) + b0
     mixed1 = torch.einsum("r,mrc->mc", w1, f1) + b1
-    grid = window_grid(W, dtype)
+    grid = window_grid(W, dtype, f0.device)
     coords0, std0 = _heat_stats(mixed0, f1, grid)
     coords1, std1 = _heat_stats(mixed1, f0, grid)
     half = W // 2

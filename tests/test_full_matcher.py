@@ -187,7 +187,7 @@ def test_matcher_low_thr_vs_reference_golden(golden, emit_bf16):
 @pytest.mark.gpu
 def test_matcher_low_thr_strict_vs_oracle_on_own_features(golden):
     """Same run, strict bar: the oracle head on the features the GPU matcher itself produced (coarse tokens
-    rounded to bf16 as the contraction sees them, the bf16 fine maps, the fp32 tokens for the window context)
+    rounded to bf16 as the coarse contraction and the window-context GEMM read them, the bf16 fine maps)
     -> ids exact under the tie rule, confidences 1e-3 relative, fine coordinates 1e-3 px.  This is the whole
     chain coarse match -> gather -> fine transformer -> fine match at 640x512 on real network features."""
     thr = float(golden["low_thr"])
@@ -213,7 +213,7 @@ def test_matcher_low_thr_strict_vs_oracle_on_own_features(golden):
            "mix_w1": sd["fine_matching.mix_feat_1.weight"].reshape(-1), "mix_b1": sd["fine_matching.mix_feat_1.bias"]}
     layers = mo.transformer_params_from_state_dict({k[len("fine."):]: v for k, v in sd.items() if k.startswith("fine.")}, 2)
     b, i, j = data["b_ids"].cpu(), data["i_ids"].cpu(), data["j_ids"].cpu()
-    w0, w1 = mo.fine_preprocess(ff0, ff1, fc0, fc1, b, i, j, hw_c, hw_c, hw_f, 7, pre)
+    w0, w1 = mo.fine_preprocess(ff0, ff1, fc0.bfloat16(), fc1.bfloat16(), b, i, j, hw_c, hw_c, hw_f, 7, pre)
     w0, w1 = mo.local_feature_transformer(w0, w1, layers, CFG["fine"]["layer_names"], CFG["fine"]["nhead"])
     r0, r1 = mo.fine_match(w0, w1, data["mkpts0_c"].cpu(), data["mkpts1_c"].cpu(), fin, hw_i, hw_f)
     compare.check_fine(data["mkpts0_f"], data["mkpts1_f"], r0, r1)

@@ -1,5 +1,5 @@
-"""Host logic of the multi-GPU path on CPU: pair / sequence sharding and the padded
-all_gather of match records with the gloo backend at world_size 2."""
+"""Host logic of the multi-GPU path on CPU: pair / sequence sharding and the exchange of match records
+(padded all_gather and gather-to-consumer) with the gloo backend at world_size 2."""
 import os
 import socket
 
@@ -47,20 +47,27 @@ def _worker(rank, world, port, capacity, counts, q):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         mine = _fake_records(rank, capacity, counts[rank])
-        out = pipeline.gather_matches(mine, capacity)
-        per_rank = pipeline.unpack_records(out, capacity, world)
-        ok = all(len(per_rank[r]) == counts[r] for r in range(world))
-        for r in range(world):
-            exp = _fake_records(r, capacity, counts[r]).numpy().view(pipeline.RECORD_DTYPE)[1:1 + counts[r]]
-            ok = ok and bool((per_rank[r] == exp).all())
+
+        def complete(out):
+            per_rank = pipeline.unpack_records(out, capacity, world)
+            good = all(len(per_rank[r]) == counts[r] for r in range(world))
+            for r in range(world):
+                exp = _fake_records(r, capacity, counts[r]).numpy().view(pipeline.RECORD_DTYPE)[1:1 + counts[r]]
+                good = good and bool((per_rank[r] == exp).all())
+            return good
+
+        ok = complete(pipeline.gather_matches(mine, capacity))            # every rank receives everything
+        for dst in range(world):                                          # only the consumer rank receives
+            out = pipeline.gather_matches(mine, capacity, dst=dst)
+            ok = ok and ((out is None) if rank != dst else complete(out))
         q.put((rank, ok))
     finally:
         dist.destroy_process_group()
 
 
 def test_gather_matches_gloo_world2():
-    """Every rank ends with every rank's records; a rank with zero matches still takes part
-    (the reference's DDP-deadlock concern, config.py:35)."""
+    """all_gather form: every rank ends with every rank's records; gather-to-consumer form (dst): only that
+    rank does.  A rank with zero matches still takes part (the reference's DDP-deadlock concern, config.py:35)."""
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
