@@ -609,6 +609,26 @@ def run_b200(args):
         torch.cuda.synchronize()
         ct_ms = fe[0].elapsed_time(fe[1]) / 3
         del o, t0f, t1f, ctm
+    # pose from matches, beside the step on the step's own match list: one batched RANSAC
+    # over the B pairs (the synthetic matches carry no two-view geometry, so this is the no-consensus worst case:
+    # every hypothesis is scored against every match, every polish runs all its rounds)
+    pose_ms = None
+    try:
+        from featurematching_b200 import pose as fm_pose
+        solver = fm_pose.PoseFromMatches(num_hypotheses=4096)
+        Kmat = torch.tensor([[520.0, 0, args.width / 2], [0, 520.0, args.height / 2], [0, 0, 1]], device=dev).expand(B, 3, 3).contiguous()
+        for _ in range(2):
+            solver.estimate(r.coarse.b_ids, r.mkpts0_f, r.mkpts1_f, Kmat, B, count=r.coarse.status, capacity=r.capacity)
+        fe = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        fe[0].record()
+        for _ in range(5):
+            solver.estimate(r.coarse.b_ids, r.mkpts0_f, r.mkpts1_f, Kmat, B, count=r.coarse.status, capacity=r.capacity)
+        fe[1].record()
+        torch.cuda.synchronize()
+        pose_ms = fe[0].elapsed_time(fe[1]) / 5
+    except Exception as ex:
+        pose_ms = None
+        sys.stderr.write(f"pose stage failed: {ex!r}\n")
     ms_step = ms_total / K
     value = world * B * K / (ms_total * 1e-3)
 
@@ -720,7 +740,8 @@ def run_b200(args):
                              "fp32 -> bf16 / NCHW -> channels-last conversions of a foreign producer are outside `value`"},
         "roofline": roofline, "kernels": kernels,
         "stage_ms": {"coarse_transformer": ct_ms, "coarse_total": stage_ms[0], "fine_gather": stage_ms[1],
-                     "fine_transformer": ft_ms, "fine_match": stage_ms[2], "pack_and_gather": stage_ms[3]},
+                     "fine_transformer": ft_ms, "fine_match": stage_ms[2], "pack_and_gather": stage_ms[3],
+                     "pose_from_matches_beside_step": pose_ms},
         "e2e": e2e, "gpu_launches": int(launches),
         "gpu_launches_note": "fm_launch_count() difference over the timed region: kernels of libfm_b200.so only (NCCL's are not counted)",
         "clocks": clocks,

@@ -192,6 +192,12 @@ cudaError_t launch_fine_transformer(const float* win0, const float* win1, const 
                                     int n_layers, const int* kinds, const float* const* layer_ptrs, float* out0,
                                     float* out1, void* workspace, int num_sms, cudaStream_t st);
 
+size_t pose_workspace_bytes(int B, int capacity, int H);
+cudaError_t launch_pose_from_matches(const int64_t* b_ids, const float* mk0, const float* mk1, int stride, const int* count,
+                                     int capacity, int B, const float* K, float thr_px, int H, int flags, uint32_t seed,
+                                     float* R, float* t, float* E, int* n_inliers, int* status, uint8_t* mask,
+                                     void* workspace, cudaStream_t st);
+
 static bool dtype_ok(int t) { return t == FM_DTYPE_BF16 || t == FM_DTYPE_F32; }
 
 static int check_coarse_args(const void* f0, const void* f1, int dt, int B, int N0, int N1, int C, int h0c, int w0c,
@@ -576,6 +582,38 @@ int fm_pack_matches_append(const int64_t* b_ids, const int64_t* i_ids, const int
                                         records, chunk_counts, chunk_index, total_capacity, sms,
                                         static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return cuda_fail(e, "pack_matches launch");
+    return FM_OK;
+}
+
+size_t fm_pose_workspace_bytes(int B, int capacity, int num_hypotheses) {
+    if (B < 1 || capacity < 0 || num_hypotheses < 1 || num_hypotheses > (1 << 20)) return 0;
+    return pose_workspace_bytes(B, capacity, num_hypotheses);
+}
+
+int fm_pose_from_matches(const int64_t* b_ids, const float* mkpts0_f, const float* mkpts1_f, int pts_stride,
+                         const int32_t* count, int capacity, int B, const float* K0, float threshold_px,
+                         int num_hypotheses, int flags, uint32_t seed, float* R, float* t, float* E, int32_t* n_inliers,
+                         int32_t* pose_status, uint8_t* inlier_mask, void* workspace, size_t workspace_bytes, void* stream) {
+    if (!b_ids || !mkpts0_f || !mkpts1_f || !K0 || !R || !t || !n_inliers || !pose_status || !workspace) {
+        set_error("null pointer argument");
+        return FM_ERR_BAD_ARG;
+    }
+    if (B < 1 || capacity < 0 || pts_stride < 2 || num_hypotheses < 1 || num_hypotheses > (1 << 20) || !(threshold_px > 0.f)) {
+        set_error("bad argument to fm_pose_from_matches (B >= 1, capacity >= 0, pts_stride >= 2, 1 <= hypotheses <= 2^20, threshold > 0)");
+        return FM_ERR_BAD_ARG;
+    }
+    if (reinterpret_cast<uintptr_t>(workspace) & 15) { set_error("workspace must be 16-byte aligned"); return FM_ERR_BAD_ARG; }
+    const size_t need = pose_workspace_bytes(B, capacity, num_hypotheses);
+    if (workspace_bytes < need) {
+        set_error("pose workspace too small: need %zu bytes, got %zu", need, workspace_bytes);
+        return FM_ERR_WORKSPACE;
+    }
+    const int sms = sm_count();
+    if (sms <= 0) { set_error("no CUDA device available (this library has no CPU path)"); return FM_ERR_CUDA; }
+    cudaError_t e = launch_pose_from_matches(b_ids, mkpts0_f, mkpts1_f, pts_stride, count, capacity, B, K0, threshold_px,
+                                             num_hypotheses, flags, seed, R, t, E, n_inliers, pose_status, inlier_mask,
+                                             workspace, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "pose_from_matches launch");
     return FM_OK;
 }
 

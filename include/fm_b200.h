@@ -227,6 +227,37 @@ FM_API int fm_pack_matches_append(const int64_t* b_ids, const int64_t* i_ids, co
                                   int32_t* chunk_counts, int chunk_index, int total_capacity,
                                   void* records, void* stream);
 
+/* ---------------------------------------------------------------- pose from matches
+ * Relative pose of every frame pair of a batch from its fine matches, on the device -- the consumer of
+ * mkpts*_f that the reference runs through OpenCV on the host after a device->host copy:
+ *   network/utils/pose_pred.py:130-151  estimate_pose: cv2.findEssentialMat(kpts0, kpts1, focal, pp, RANSAC,
+ *                                       0.999, 1.0) + cv2.recoverPose(E, kpts0, kpts1, np.eye(3), 1e9, mask)
+ *   network/utils/pose_pred.py:170-179  get_opencv_pose (R = I, t = 0 when no pose comes out)
+ *   utils/metrics.py:79-109,124-159     the same per batch element (mask = m_bids == bs)
+ * b_ids int64[capacity] sorted ascending (as fm_coarse_match emits them); mkpts0_f / mkpts1_f float rows of
+ * `pts_stride` floats (3 for the head's [M, 3] outputs, 2 for plain [M, 2]); count = device match count or
+ * NULL (= capacity); K0 float[B, 9] row-major intrinsics of image 0 per pair -- like the reference, focal =
+ * (fx + fy) / 2 and the principal point of K0 normalise BOTH images; threshold_px = RANSAC threshold in pixels
+ * (the reference: 1.0).  A match is an inlier iff its Sampson error <= (threshold_px / focal)^2 (OpenCV's
+ * definition).  num_hypotheses 8-point samples per pair (4096 recommended), deterministic in `seed`.
+ * flags:  FM_POSE_POLISH       least-squares local optimisation of the best hypotheses (recommended; OpenCV
+ *                              returns its minimal-sample model unrefined)
+ *         FM_POSE_IDENTITY_K   rank the (R, +-t) candidates on PIXEL coordinates with an identity camera matrix,
+ *                              exactly as the reference's recoverPose call does; without it the normalised
+ *                              coordinates are used (what cv2.recoverPose(E, p0, p1, K) computes)
+ * Outputs per pair: R float[B, 9] row-major, t float[B, 3] unit vector, E float[B, 9] (may be NULL), n_inliers,
+ * pose_status (0 = ok, 1 = fewer than 8 matches, 2 = no sample gave a model; R = I, t = 0 for 1 and 2) and,
+ * if not NULL, inlier_mask uint8[capacity] aligned with the match list.
+ * workspace: fm_pose_workspace_bytes(B, capacity, num_hypotheses) bytes, 16-byte aligned. */
+#define FM_POSE_POLISH 1
+#define FM_POSE_IDENTITY_K 2
+FM_API size_t fm_pose_workspace_bytes(int B, int capacity, int num_hypotheses);
+FM_API int fm_pose_from_matches(const int64_t* b_ids, const float* mkpts0_f, const float* mkpts1_f, int pts_stride,
+                                const int32_t* count, int capacity, int B, const float* K0, float threshold_px,
+                                int num_hypotheses, int flags, uint32_t seed, float* R, float* t, float* E,
+                                int32_t* n_inliers, int32_t* pose_status, uint8_t* inlier_mask, void* workspace,
+                                size_t workspace_bytes, void* stream);
+
 /* ---------------------------------------------------------------- test / profiling hooks
  * Same contract as fm_coarse_match, but the score statistics come from a plain SIMT kernel
  * instead of the tcgen05 kernel.  Exists so tests can tell a tensor-core plumbing bug from a

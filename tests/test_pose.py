@@ -1,0 +1,191 @@
+"""Pose from matches: csrc/pose_ransac.cu against OpenCV as the reference calls it
+(network/utils/pose_pred.py:130-151).  RANSAC is randomised on both sides, so parity is defined on the OUTCOME, on
+synthetic two-view geometry with planted inliers (tests/pose_scenes.py):
+  * noise-free: inlier-set IoU >= 0.99, rotation and translation direction (sign included) within 1e-3 rad of cv2;
+  * with pixel noise (no exact answer): at least as many inliers as cv2 minus 2 %, pose error against the planted
+    truth no worse than 1.5x cv2's + 2e-3 rad.
+CPU: the same arithmetic (csrc/fm_pose_math.cuh) built for the host by g++ (tests/pose_hostcheck.cpp).
+GPU: the kernels through the C ABI, batched."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+from tests import pose_scenes as ps
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CASES = [(0, 2000, 0.1), (1, 2000, 0.2), (2, 1500, 0.3), (3, 900, 0.4), (4, 300, 0.2), (5, 60, 0.1)]
+
+
+@pytest.fixture(scope="module")
+def hostlib(tmp_path_factory):
+    so = str(tmp_path_factory.mktemp("pose") / "libposecheck.so")
+    subprocess.run(["g++", "-O2", "-shared", "-fPIC", "-o", so, os.path.join(ROOT, "tests", "pose_hostcheck.cpp")], check=True)
+    return ctypes.CDLL(so)
+
+
+def host_pose(lib, x0, x1, K, H, flags, seed=1):
+    M = len(x0)
+    R, t, E = np.zeros(9, np.float32), np.zeros(3, np.float32), np.zeros(9, np.float32)
+    n, mask = ctypes.c_int(0), np.zeros(M, np.uint8)
+    Kf = np.ascontiguousarray(K.astype(np.float32).reshape(-1))
+    vp = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    rc = lib.pose_hostcheck(vp(x0), vp(x1), M, vp(Kf), ctypes.c_float(1.0), H, flags, seed, vp(R), vp(t), vp(E),
+                            ctypes.byref(n), vp(mask))
+    return rc, R.reshape(3, 3).astype(np.float64), t.astype(np.float64), mask > 0, n.value
+
+
+def check_noise_free(R, t, mask, ref, inl):
+    Rc, tc, mc = ref
+    iou = (mask & mc).sum() / max((mask | mc).sum(), 1)
+    assert iou >= 0.99, f"inlier IoU {iou:.4f}"
+    assert (mask & inl).sum() / max((mask | inl).sum(), 1) >= 0.99
+    assert ps.rot_angle(Rc, R) <= 1e-3, f"rotation differs from cv2 by {ps.rot_angle(Rc, R):.2e} rad"
+    assert ps.vec_angle(tc, t) <= 1e-3, f"translation direction differs from cv2 by {ps.vec_angle(tc, t):.2e} rad"
+
+
+# ------------------------------------------------------------------------------ CPU: host build of the arithmetic
+@pytest.mark.parametrize("identity_k", [True, False], ids=["reference_call", "with_K"])
+@pytest.mark.parametrize("polish", [False, True], ids=["minimal", "polished"])
+@pytest.mark.parametrize("case", CASES)
+def test_host_arithmetic_vs_cv2_noise_free(hostlib, case, polish, identity_k):
+    seed, M, outlier = case
+    K, R, t, x0, x1, inl = ps.scene(seed, M, outlier)
+    ref = ps.reference_estimate_pose(x0, x1, K, identity_k)
+    rc, Rm, tm, mask, n = host_pose(hostlib, x0, x1, K, 1024, (1 if polish else 0) | (2 if identity_k else 0))
+    assert rc == 0
+    check_noise_free(Rm, tm, mask, ref, inl)
+    if not identity_k:   # with the camera matrix the cheirality test is meaningful: the planted pose comes back
+        assert ps.rot_angle(R, Rm) <= 1e-3 and ps.vec_angle(t, tm) <= 1e-3
+
+
+@pytest.mark.parametrize("case", [(10, 2000, 0.1, 0.5), (11, 2000, 0.3, 0.5), (12, 1200, 0.4, 0.5), (13, 2000, 0.2, 1.0)])
+def test_host_arithmetic_with_pixel_noise(hostlib, case):
+    seed, M, outlier, noise = case
+    K, R, t, x0, x1, inl = ps.scene(seed, M, outlier, noise=noise)
+    Rc, tc, mc = ps.reference_estimate_pose(x0, x1, K, identity_k=False)
+    rc, Rm, tm, mask, n = host_pose(hostlib, x0, x1, K, 4096, 1)
+    assert rc == 0
+    assert n >= 0.98 * mc.sum()
+    assert ps.rot_angle(R, Rm) <= 1.5 * ps.rot_angle(R, Rc) + 2e-3
+    assert ps.vec_angle(t, tm) <= 1.5 * ps.vec_angle(t, tc) + 2e-2
+    assert (mask & ~inl).sum() <= 0.02 * max(mask.sum(), 1)      # planted outliers stay out
+
+
+def test_rotation_to_euler_matches_reference_formula():
+    from featurematching_b200 import pose
+    import math
+    rs = np.random.RandomState(0)
+    import cv2
+    for k in range(20):
+        R, _ = cv2.Rodrigues(rs.uniform(-2, 2, 3))
+        if k == 0:
+            R = np.array([[0, 0, 1.0], [0, 1, 0], [-1, 0, 0]])   # sy = 0: the singular branch (pose_pred.py:121-124)
+        sy = math.sqrt(R[0, 0] ** 2 + R[1, 0] ** 2)
+        if sy >= 1e-6:
+            ref = [math.atan2(R[2, 1], R[2, 2]), math.atan2(-R[2, 0], sy), math.atan2(R[1, 0], R[0, 0])]
+        else:
+            ref = [math.atan2(-R[1, 2], R[1, 1]), math.atan2(-R[2, 0], sy), 0.0]
+        got = pose.rotation_to_euler(torch.from_numpy(R)[None])[0].numpy()
+        np.testing.assert_allclose(got, ref, atol=1e-12)
+
+
+# ------------------------------------------------------------------------------ GPU: the kernels through the C ABI
+def batch(cases, noise=0.0, pad=37):
+    rows = [ps.scene(s, M, o, noise=noise) for s, M, o in cases]
+    b_ids = np.concatenate([np.full(len(r[3]), k, np.int64) for k, r in enumerate(rows)])
+    # the head's layout: [M, 3] rows (x, y, std); capacity-padded buffers with the count on the device
+    p0 = np.concatenate([np.concatenate([r[3], np.full((len(r[3]), 1), 0.5, np.float32)], 1) for r in rows])
+    p1 = np.concatenate([np.concatenate([r[4], np.full((len(r[4]), 1), 0.5, np.float32)], 1) for r in rows])
+    M = len(b_ids)
+    padf = lambda a, v: np.concatenate([a, np.full((pad,) + a.shape[1:], v, a.dtype)])
+    K = np.stack([r[0] for r in rows]).astype(np.float32)
+    return rows, M, padf(b_ids, 0), padf(p0, np.nan), padf(p1, np.nan), K
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("identity_k", [True, False], ids=["reference_call", "with_K"])
+@pytest.mark.parametrize("polish", [False, True], ids=["minimal", "polished"])
+def test_gpu_pose_batch_vs_cv2_noise_free(polish, identity_k):
+    from featurematching_b200 import pose
+    dev = "cuda:0"
+    cases = CASES + [(6, 7, 0.0), (7, 2000, 0.25)]      # pair 6: seven matches -> no pose, like the reference's None
+    rows, M, b_ids, p0, p1, K = batch(cases)
+    solver = pose.PoseFromMatches(num_hypotheses=1024, polish=polish, identity_k=identity_k, seed=3)
+    count = torch.tensor([M], dtype=torch.int32, device=dev)
+    out = solver.estimate(torch.from_numpy(b_ids).to(dev), torch.from_numpy(p0).to(dev), torch.from_numpy(p1).to(dev),
+                          torch.from_numpy(K).to(dev), len(cases), count=count)
+    torch.cuda.synchronize()
+    R, t, st = out["R"].cpu().numpy().astype(np.float64), out["t"].cpu().numpy().astype(np.float64), out["status"].cpu().numpy()
+    mask, ninl = out["inlier_mask"].cpu().numpy() > 0, out["n_inliers"].cpu().numpy()
+    lo = 0
+    for k, (Kk, Rk, tk, x0, x1, inl) in enumerate(rows):
+        n = len(x0)
+        if n < 8:
+            assert st[k] == 1 and np.array_equal(R[k], np.eye(3)) and not t[k].any() and ninl[k] == 0
+        else:
+            assert st[k] == 0
+            ref = ps.reference_estimate_pose(x0, x1, Kk, identity_k)
+            check_noise_free(R[k], t[k], mask[lo:lo + n], ref, inl)
+            assert ninl[k] == mask[lo:lo + n].sum()
+            E = out["E"][k].cpu().numpy().astype(np.float64)
+            sv = np.linalg.svd(E, compute_uv=False)
+            assert abs(sv[0] - sv[1]) < 1e-4 and sv[2] < 1e-4          # an essential matrix
+        lo += n
+    assert not mask[M:].any()                                          # padding untouched
+    # deterministic in the seed
+    out2 = solver.estimate(torch.from_numpy(b_ids).to(dev), torch.from_numpy(p0).to(dev), torch.from_numpy(p1).to(dev),
+                           torch.from_numpy(K).to(dev), len(cases), count=count)
+    assert torch.equal(out2["R"], out["R"]) and torch.equal(out2["inlier_mask"], out["inlier_mask"])
+
+
+@pytest.mark.gpu
+def test_gpu_pose_with_pixel_noise_beats_or_matches_cv2():
+    from featurematching_b200 import pose
+    dev = "cuda:0"
+    cases = [(10, 2000, 0.1), (11, 2000, 0.3), (12, 1200, 0.4), (13, 2000, 0.2), (14, 3900, 0.15)]
+    rows, M, b_ids, p0, p1, K = batch(cases, noise=0.5, pad=0)
+    solver = pose.PoseFromMatches(num_hypotheses=4096, polish=True, identity_k=False, seed=5)
+    out = solver.estimate(torch.from_numpy(b_ids).to(dev), torch.from_numpy(p0).to(dev), torch.from_numpy(p1).to(dev),
+                          torch.from_numpy(K).to(dev), len(cases))
+    R, t = out["R"].cpu().numpy().astype(np.float64), out["t"].cpu().numpy().astype(np.float64)
+    mask = out["inlier_mask"].cpu().numpy() > 0
+    lo = 0
+    for k, (Kk, Rk, tk, x0, x1, inl) in enumerate(rows):
+        n = len(x0)
+        Rc, tc, mc = ps.reference_estimate_pose(x0, x1, Kk, identity_k=False)
+        assert mask[lo:lo + n].sum() >= 0.98 * mc.sum()
+        assert ps.rot_angle(Rk, R[k]) <= 1.5 * ps.rot_angle(Rk, Rc) + 2e-3
+        assert ps.vec_angle(tk, t[k]) <= 1.5 * ps.vec_angle(tk, tc) + 2e-2
+        assert (mask[lo:lo + n] & ~inl).sum() <= 0.02 * max(mask[lo:lo + n].sum(), 1)
+        lo += n
+
+
+@pytest.mark.gpu
+def test_gpu_get_opencv_pose_drop_in():
+    """pose.get_opencv_pose vs the reference's Pose_Pred.get_opencv_pose arithmetic on cv2's own (R, t)
+    (pose_pred.py:170-190): four [1, 1, 3] tensors, Euler angles reversed, inverse pose."""
+    import math
+    from featurematching_b200 import pose
+    dev = "cuda:0"
+    K, R, t, x0, x1, inl = ps.scene(21, 1500, 0.2)
+    data = {"mkpts0_f": torch.from_numpy(np.concatenate([x0, np.ones((len(x0), 1), np.float32)], 1)).to(dev),
+            "mkpts1_f": torch.from_numpy(np.concatenate([x1, np.ones((len(x1), 1), np.float32)], 1)).to(dev),
+            "K0": torch.from_numpy(K.astype(np.float32))[None].to(dev)}
+    aa, tr, aa_inv, tr_inv = pose.get_opencv_pose(data, pose.PoseFromMatches(num_hypotheses=1024, polish=False))
+    assert aa.shape == (1, 1, 3) and tr.shape == (1, 1, 3) and aa_inv.shape == (1, 1, 3) and tr_inv.shape == (1, 1, 3)
+    Rc, tc, _ = ps.reference_estimate_pose(x0, x1, K, identity_k=True)
+
+    def euler(Rm):
+        sy = math.sqrt(Rm[0, 0] ** 2 + Rm[1, 0] ** 2)
+        return np.array([math.atan2(Rm[2, 1], Rm[2, 2]), math.atan2(-Rm[2, 0], sy), math.atan2(Rm[1, 0], Rm[0, 0])])
+    np.testing.assert_allclose(aa[0, 0].cpu().numpy(), euler(Rc)[::-1], atol=1e-3)
+    np.testing.assert_allclose(tr[0, 0].cpu().numpy(), tc, atol=2e-3)
+    np.testing.assert_allclose(aa_inv[0, 0].cpu().numpy(), euler(np.linalg.inv(Rc))[::-1], atol=1e-3)
+    np.testing.assert_allclose(tr_inv[0, 0].cpu().numpy(), -tc, atol=2e-3)
+    few = {k: (v[:3] if k != "K0" else v) for k, v in data.items()}
+    aa, tr, _, _ = pose.get_opencv_pose(few)
+    assert not aa.any() and not tr.any()          # fewer than 5 matches: R = I, t = 0 (pose_pred.py:131-132,177-179)
