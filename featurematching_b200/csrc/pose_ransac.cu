@@ -101,6 +101,14 @@ __global__ void __launch_bounds__(kPoseThreads) pose_prepare_kernel(PoseParams p
 }
 
 // ---- 2. one thread = one hypothesis
+// The three steps are kept as separate device functions: inlined into one body (sample8 -> null_vector_8x9 ->
+// early return -> project_essential) nvcc 12.9 -O3 for sm_100a produced a kernel whose pivot test rejected EVERY
+// sample on the device (tools/probe_pose_null.cu: 0 / 1024 models where the host build and every partial
+// inlining give 1024 / 1024).
+__device__ __noinline__ void sample8_dev(uint32_t seed, int b, int h, int n, int* idx) { sample8(seed, b, h, n, idx); }
+__device__ __noinline__ bool null_vector_dev(float* A, float* e) { return null_vector_8x9(A, e); }
+__device__ __noinline__ void project_essential_dev(float* e) { project_essential(e); }
+
 __global__ void __launch_bounds__(128) pose_hypotheses_kernel(PoseParams p, PoseWs w) {
     const int b = blockIdx.y, h = blockIdx.x * blockDim.x + threadIdx.x;
     if (h >= p.H) return;
@@ -110,14 +118,14 @@ __global__ void __launch_bounds__(128) pose_hypotheses_kernel(PoseParams p, Pose
     *cost = INFINITY;                     // scored (overwritten) only if a model comes out
     if (n < 8) return;
     int idx[8];
-    sample8(p.seed, b, h, n, idx);
+    sample8_dev(p.seed, b, h, n, idx);
     float A[72], e[9];
     for (int k = 0; k < 8; ++k) {
         const float4 q = w.pts[lo + idx[k]];
         epipolar_row(q.x, q.y, q.z, q.w, A + 9 * k);
     }
-    if (!null_vector_8x9(A, e)) { E[0] = NAN; return; }
-    project_essential(e);
+    if (!null_vector_dev(A, e)) { E[0] = NAN; return; }
+    project_essential_dev(e);
     for (int i = 0; i < 9; ++i) E[i] = e[i];
     *cost = 0.f;                          // marks "valid" for the scoring kernel
 }
