@@ -7,7 +7,8 @@ import ctypes
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libfm_b200.so")
+# FM_B200_LIB: developer switch for A/B builds of the same library (tools/ab_build.sh); the product is libfm_b200.so
+LIB_PATH = os.environ.get("FM_B200_LIB") or os.path.join(HERE, "libfm_b200.so")
 
 FM_OK = 0
 DTYPE_BF16, DTYPE_F32 = 0, 1

@@ -121,6 +121,33 @@ __device__ __forceinline__ void layer_norm32(float (&v)[32], float2 mine, float2
     }
 }
 
+// -DTF_TRACE: clock64 stamps of CTA 0 (warp 0 of each slot + the slot's MMA thread) for tools/dbg_tf_trace.py
+#ifdef TF_TRACE
+constexpr int kTrTiles = 64, kTrPts = 32;
+__device__ long long g_tf_trace[2][2][kTrTiles][kTrPts];   // [role: epilogue, mma][slot][tile][point]
+#define TFT(role, slot, n, id) do { if (blockIdx.x == 0 && (n) < kTrTiles) g_tf_trace[role][slot][n][id] = clock64(); } while (0)
+#else
+#define TFT(role, slot, n, id) do {} while (0)
+#endif
+
+// Hand-off waits: mbarrier.try_wait with a suspend-time hint -- the hardware parks the warp until the phase completes
+// or the hint expires, so a waiting warp neither burns issue slots nor oversleeps (try_wait + nanosleep(64) back-off
+// measured 2 % slower: r02 A/B, tools/gpu_ab_tf.sh).  -DTF_WAIT_HINT=0 restores the back-off loop.
+#ifndef TF_WAIT_HINT
+#define TF_WAIT_HINT 1000
+#endif
+template <int kSleepNs>
+__device__ __forceinline__ void tf_wait(uint64_t* bar, uint32_t parity) {
+#if TF_WAIT_HINT > 0
+    uint32_t spins = 0;
+    while (!mbar_try_wait_hint(bar, parity, TF_WAIT_HINT)) {
+        if (++spins > 20000000u) __trap();   // protocol bug -> launch failure, not a hung GPU
+    }
+#else
+    mbar_wait_backoff<kSleepNs>(bar, parity);
+#endif
+}
+
 struct __align__(16) TfCtl {
     uint64_t w_full;
     uint64_t to_epi[2];     // MMA warp -> the slot's epilogue warps (tcgen05.commit)
@@ -197,7 +224,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
             const uint64_t d_qkv = umma_desc_k_sw128(wb + kOffQkv), d_merge = umma_desc_k_sw128(wb + kOffMerge),
                            d_mlp0 = umma_desc_k_sw128(wb + kOffMlp0), d_mlp2 = umma_desc_k_sw128(wb + kOffMlp2);
             uint32_t it = 0;
-            auto wait_ops = [&]() { mbar_wait_backoff<20>(&ctl->to_mma[slot], it & 1); ++it; tc_fence_after(); };
+            auto wait_ops = [&]() { tf_wait<20>(&ctl->to_mma[slot], it & 1); ++it; tc_fence_after(); };
             // D[., n0 .. n0 + N) (+)= X operand (K = 64) x rows [n0, n0 + N) of Wqkv, three split terms.
             // term 0: a_hi b_hi, term 1: a_hi b_lo, term 2: a_lo b_hi.  The loops over terms are NOT
             // unrolled and descriptors are base + offset: fully unrolled, the 72 descriptors of a pass
@@ -214,17 +241,21 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                 umma_commit(done);
             };
             mbar_wait(&ctl->w_full, 0);
-            for (int item = blockIdx.x * 2 + slot; item < items; item += 2 * gridDim.x) {
+            [[maybe_unused]] int tn = 0;
+            for (int item = blockIdx.x * 2 + slot; item < items; item += 2 * gridDim.x, ++tn) {
                 for (int pass = 0; pass < kPasses; ++pass) {
+                    [[maybe_unused]] const int tb = 8 * pass;
                     if (kCross) {
                         // K | V of the source rows, then -- after the operand swap -- Q of the rows to
                         // update: the Q batch runs while the epilogue reduces K^T V
                         wait_ops(); project(64, id128, &ctl->to_epi[slot]);
                         wait_ops(); project(0, id64, &ctl->q_done[slot]);
                     } else {
-                        wait_ops(); project(0, id192, &ctl->to_epi[slot]);   // Q | K | V
+                        wait_ops(); TFT(1, slot, tn, tb + 0); project(0, id192, &ctl->to_epi[slot]);   // Q | K | V
+                        TFT(1, slot, tn, tb + 1);
                     }
                     wait_ops();   // message ready: merge
+                    TFT(1, slot, tn, tb + 2);
 #pragma unroll 1
                     for (int term = 0; term < 3; ++term) {
                         const uint32_t a = ts + (term == 2 ? 160 : 128);
@@ -233,7 +264,9 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                         for (int k = 0; k < 4; ++k) umma_bf16_ts(ts, a + 8 * k, b + 2 * k, id64, (term | k) != 0);
                     }
                     umma_commit(&ctl->to_epi[slot]);
+                    TFT(1, slot, tn, tb + 3);
                     wait_ops();   // LayerNorm-1 output ready: hidden = [x | msg] Wmlp0^T
+                    TFT(1, slot, tn, tb + 4);
 #pragma unroll 1
                     for (int term = 0; term < 3; ++term)
 #pragma unroll 1
@@ -244,7 +277,9 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                             for (int k = 0; k < 4; ++k) umma_bf16_ts(ts, a + 8 * k, b + 2 * k, id128, (term | kc | k) != 0);
                         }
                     umma_commit(&ctl->to_epi[slot]);
+                    TFT(1, slot, tn, tb + 5);
                     wait_ops();   // relu(hidden) ready: out = hidden Wmlp2^T
+                    TFT(1, slot, tn, tb + 6);
 #pragma unroll 1
                     for (int term = 0; term < 3; ++term)
 #pragma unroll 1
@@ -255,6 +290,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                             for (int k = 0; k < 4; ++k) umma_bf16_ts(ts, a + 8 * k, b + 2 * k, id64, (term | kc | k) != 0);
                         }
                     umma_commit(&ctl->to_epi[slot]);
+                    TFT(1, slot, tn, tb + 7);
                 }
             }
         }
@@ -272,7 +308,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
         float* kvm = kvm_all + slot * 2 * 64 * 8;                  // this slot's KV matrices / key sums
         float* ksum = ksum_all + slot * 2 * 64;
         uint32_t it = 0, itq = 0;
-        auto wait_acc = [&]() { mbar_wait_backoff<64>(&ctl->to_epi[slot], it & 1); ++it; tc_fence_after(); };
+        auto wait_acc = [&]() { tf_wait<64>(&ctl->to_epi[slot], it & 1); ++it; tc_fence_after(); };
         auto signal_mma = [&]() {
             tmem_st_wait();
             tc_fence_before();
@@ -297,8 +333,12 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
         };
         mbar_wait(&ctl->w_full, 0);   // LayerNorm parameters live in the blob
 
-        for (int item = blockIdx.x * 2 + slot; item < items; item += 2 * gridDim.x) {
+        [[maybe_unused]] int tn = 0;
+        [[maybe_unused]] const bool tr = (warp & 7) == 0 && lane == 0;
+#define TFE(id) do { if (tr) TFT(0, slot, tn, 16 * pass + (id)); } while (0)
+        for (int item = blockIdx.x * 2 + slot; item < items; item += 2 * gridDim.x, ++tn) {
             const int next = item + 2 * gridDim.x;
+            { [[maybe_unused]] const int pass = 0; TFE(0); }
             // match of this thread's row; self: both windows of one match, cross: same side of two matches
             const int m = kCross ? 2 * item + w : item;
             const bool valid = r < WW && m < M;
@@ -315,26 +355,28 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                 signal_mma();
                 if (next < items) prefetch_rows(w, next);
             }
+            { [[maybe_unused]] const int pass = 0; TFE(1); }
 
 #pragma unroll 1
             for (int pass = 0; pass < kPasses; ++pass) {
                 // ================= attention: K, V -> per-window KV matrices =================
                 wait_acc();   // self: Q | K | V ready; cross: K | V of the source rows
+                TFE(2);
                 float qf[32];
                 uint32_t v[32];
-                if (!kCross) {   // Q first: its conversion overlaps the wait for the scratch lock
-                    tmem_ld_32x32(tl + 32 * g, v);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) qf[i] = elu1(__uint_as_float(v[i]));
-                } else {
+                if (kCross) {
                     // K | V of the source rows are in the accumulators, their operand is free: the rows
                     // to update take the tile now, and their Q projection runs under the K^T V phase
                     store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
                     signal_mma();
                 }
+                // (nothing of the residual stream is held in registers across the attention phases: the K^T V
+                // reduction and the message are chains of shared-memory loads whose latency only hides if the
+                // compiler has registers to keep a dozen of them in flight -- with x[32] and Q[32] live they ran
+                // at 45 and 72 cycles per iteration (tools/dbg_tf_trace.py); x is re-read from L2 before LayerNorm 2)
                 // The K | V scratch is shared by the two slots: held until this slot's K^T V sums are
                 // done (every warp signs off after its last scratch read).
+                TFE(3);
                 if (st == 0) {
                     uint32_t spins = 0;
                     while (atomicCAS(&ctl->lock_owner, 0, slot + 1) != 0) {
@@ -344,6 +386,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     ctl->lock_left = 8;
                 }
                 named_bar_sync(bar_id, kSlotThreads);
+                TFE(4);
                 {
                     uint8_t* rowp = scr + (w * kMaxWW + (r < WW ? r : 0)) * kScrRow;
                     tmem_ld_32x32(tl + 64 + 32 * g, v);
@@ -365,6 +408,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     }
                 }
                 named_bar_sync(bar_id, kSlotThreads);
+                TFE(5);
                 {   // KV[d][v] = sum_r K[r][d] V[r][v] within a head; thread = (window, d, half of the 8 v)
                     const int w2 = st >> 7, d = (st & 127) >> 1, vh = st & 1;
                     const uint8_t* kp = scr + w2 * kMaxWW * kScrRow + d * 4;
@@ -393,16 +437,18 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     __threadfence_block();
                     if (atomicSub(&ctl->lock_left, 1) == 1) atomicExch(&ctl->lock_owner, 0);
                 }
+                TFE(6);
                 if (kCross) {
-                    mbar_wait_backoff<64>(&ctl->q_done[slot], itq & 1);   // Q (ran under the K^T V phase)
+                    tf_wait<64>(&ctl->q_done[slot], itq & 1);   // Q (ran under the K^T V phase)
                     ++itq;
                     tc_fence_after();
-                    tmem_ld_32x32(tl + 32 * g, v);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) qf[i] = elu1(__uint_as_float(v[i]));
                 }
+                tmem_ld_32x32(tl + 32 * g, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) qf[i] = elu1(__uint_as_float(v[i]));
                 named_bar_sync(bar_id, kSlotThreads);   // KV matrices visible
+                TFE(7);
                 // ================= message = (Q KV) / (Q sum K + eps)  (attentions.py:42-44) =================
 #pragma unroll
                 for (int hh = 0; hh < 4; ++hh) {
@@ -438,8 +484,10 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     tmem_st_32x4(tl + 160 + 16 * g + 4 * hh, lo);
                 }
                 signal_mma();
+                TFE(8);
                 // ================= merge -> LayerNorm 1 =================
                 wait_acc();
+                TFE(9);
                 float y[32];
                 tmem_ld_32x32(tl + 32 * g, v);
                 tmem_ld_wait();
@@ -451,8 +499,10 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                 layer_norm32(y, mine, lnrow[g ^ 1], ln, ln + 64);
                 store_operand32(tl + 128 + 16 * g, tl + 160 + 16 * g, y);
                 signal_mma();
+                TFE(10);
                 // ================= MLP hidden: relu =================
                 wait_acc();
+                TFE(11);
 #pragma unroll
                 for (int half = 0; half < 2; ++half) {
                     tmem_ld_32x32(tl + 64 * g + 32 * half, v);
@@ -462,8 +512,11 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     store_operand32(tl + 192 + 32 * g + 16 * half, tl + 128 + 32 * g + 16 * half, y);
                 }
                 signal_mma();
+                TFE(12);
                 // ================= MLP out -> LayerNorm 2 -> residual =================
+                load_rows(x, kCross ? pass : w, m);   // the rows being updated, again (L2): in flight under the MLP-2 batch
                 wait_acc();
+                TFE(13);
                 tmem_ld_32x32(tl + 32 * g, v);
                 tmem_ld_wait();
 #pragma unroll
@@ -474,6 +527,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                 layer_norm32(y, mine, lnrow[g ^ 1], ln + 128, ln + 192);
 #pragma unroll
                 for (int i = 0; i < 32; ++i) x[i] += y[i];
+                TFE(14);
                 if (kCross && pass == 0) {
                     // the updated image-0 windows are the K | V source of pass 1 (transformer.py:95)
                     store_operand32(tl + 192 + 16 * g, tl + 224 + 16 * g, x);
@@ -485,6 +539,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                     for (int c = 0; c < 4; ++c) stg256(dst, x, 8 * c);
                 }
                 if (kCross && pass == 0) load_rows(x, 1, m);   // pass 1 updates the image-1 windows
+                TFE(15);
             }
         }
     }
@@ -537,5 +592,11 @@ cudaError_t launch_fine_transformer(const float* win0, const float* win1, const 
     }
     return cudaSuccess;
 }
+
+#ifdef TF_TRACE
+extern "C" __attribute__((visibility("default"))) int fm_debug_tf_trace(long long* host_out) {
+    return static_cast<int>(cudaMemcpyFromSymbol(host_out, g_tf_trace, sizeof(g_tf_trace)));
+}
+#endif
 
 }  // namespace fm
