@@ -828,6 +828,7 @@ def run_job(args):
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     launches0 = lib.fm_launch_count()
     torch.cuda.synchronize()
+    t_host0 = time.perf_counter()
     ev[0].record()
     for k in range(steps):
         r, _ = step_loop(args, head, ftm, og, lib, rank, B, lambda _k, kk=k: inputs(kk), shp, 1, stage_events=False,
@@ -836,13 +837,17 @@ def run_job(args):
     if og:
         og.finish()
     ev[1].record()
+    host_ms = (time.perf_counter() - t_host0) * 1e3   # host-side enqueue time of the whole job (no sync inside)
     torch.cuda.synchronize()
     ms = ev[0].elapsed_time(ev[1])
     launches = lib.fm_launch_count() - launches0
+    per_rank = [[ms, host_ms]]
     if world > 1:
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+        allr = torch.zeros(world, 2, device=dev)
+        allr[rank, 0], allr[rank, 1] = ms, host_ms
+        dist.all_reduce(allr)
+        per_rank = allr.tolist()
+        ms = max(r[0] for r in per_rank)
         dist.barrier()
     clocks = sampler.stop() if sampler else None
     flags = int(r.coarse.status[_lib.ST_FLAGS].item())
@@ -863,7 +868,9 @@ def run_job(args):
                                        + (", records to rank 0 behind each step" if world > 1 else ""),
                            "N0": N, "N1": N, "C": 256, "fine_map": [64, hw_f[0], hw_f[1]], "pairs_rank0": n_pairs,
                            "matches_total": int(matches[0]), "l2": "every step reads new frames (no reuse between steps)"},
-                "gpu_launches": int(launches), "clocks": clocks}
+                "gpu_launches": int(launches), "clocks": clocks,
+                "per_rank_ms": [round(r[0], 2) for r in per_rank],
+                "per_rank_host_enqueue_ms": [round(r[1], 2) for r in per_rank]}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
