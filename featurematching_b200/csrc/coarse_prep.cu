@@ -24,39 +24,62 @@ __global__ void __launch_bounds__(256) coarse_prep_kernel(const void* __restrict
     const int N = side ? N1 : N0;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const void* src = side ? f1 : f0;
-    __nv_bfloat16* dst = side ? f1b : f0b;
+    [[maybe_unused]] __nv_bfloat16* dst = side ? f1b : f0b;
     float wmax = 0.f;
-    for (int rr = 0; rr < 4; ++rr) {
-        const int row = blockIdx.x * kRowsPerBlock + warp * 4 + rr;
-        if (row >= N) break;
-        const size_t base = (static_cast<size_t>(b) * N + row) * C;
-        float ss = 0.f;
-        if (lane * 8 < C) {
-            __nv_bfloat162 v[4];
-            if constexpr (kF32In) {
-                const float4* p = reinterpret_cast<const float4*>(static_cast<const float*>(src) + base) + lane * 2;
-                float4 a = __ldg(p), c = __ldg(p + 1);
-                v[0] = __floats2bfloat162_rn(a.x, a.y);
-                v[1] = __floats2bfloat162_rn(a.z, a.w);
-                v[2] = __floats2bfloat162_rn(c.x, c.y);
-                v[3] = __floats2bfloat162_rn(c.z, c.w);
-                *reinterpret_cast<uint4*>(dst + base + lane * 8) = *reinterpret_cast<uint4*>(v);
-            } else {
-                uint4 raw = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(src) + base) + lane);
-                *reinterpret_cast<uint4*>(v) = raw;
-            }
+    // the warp's four rows: all loads first (one 16-byte load per lane and row; issued one row after the other the
+    // kernel ran at 39 us for 168 MB = 65 % of the copy bandwidth)
+    const int row_base = blockIdx.x * kRowsPerBlock + warp * 4;
+    const bool lane_ok = lane * 8 < C;
+    __nv_bfloat162 v[4][4];
+    if constexpr (kF32In) {
+        float4 a[4], c[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                float2 f = __bfloat1622float2(v[k]);
-                ss = fmaf(f.x, f.x, ss);
-                ss = fmaf(f.y, f.y, ss);
+        for (int rr = 0; rr < 4; ++rr) {
+            const int row = row_base + rr;
+            if (row < N && lane_ok) {
+                const float4* p = reinterpret_cast<const float4*>(static_cast<const float*>(src) + (static_cast<size_t>(b) * N + row) * C) + lane * 2;
+                a[rr] = __ldg(p); c[rr] = __ldg(p + 1);
+            } else {
+                a[rr] = make_float4(0.f, 0.f, 0.f, 0.f); c[rr] = a[rr];
             }
+        }
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr) {
+            v[rr][0] = __floats2bfloat162_rn(a[rr].x, a[rr].y);
+            v[rr][1] = __floats2bfloat162_rn(a[rr].z, a[rr].w);
+            v[rr][2] = __floats2bfloat162_rn(c[rr].x, c[rr].y);
+            v[rr][3] = __floats2bfloat162_rn(c[rr].z, c[rr].w);
+            const int row = row_base + rr;
+            if (row < N && lane_ok)
+                *reinterpret_cast<uint4*>(dst + (static_cast<size_t>(b) * N + row) * C + lane * 8) = *reinterpret_cast<uint4*>(v[rr]);
+        }
+    } else {
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr) {
+            const int row = row_base + rr;
+            uint4 raw = make_uint4(0u, 0u, 0u, 0u);
+            if (row < N && lane_ok)
+                raw = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(src) + (static_cast<size_t>(b) * N + row) * C) + lane);
+            *reinterpret_cast<uint4*>(v[rr]) = raw;
+        }
+    }
+#pragma unroll
+    for (int rr = 0; rr < 4; ++rr) {
+        const int row = row_base + rr;
+        float ss = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            float2 f = __bfloat1622float2(v[rr][k]);
+            ss = fmaf(f.x, f.x, ss);
+            ss = fmaf(f.y, f.y, ss);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
         const float n = sqrtf(ss);
-        if (side == 0 && lane == 0) norm0[static_cast<size_t>(b) * N0pad + row] = n;
-        wmax = fmaxf(wmax, n);
+        if (row < N) {
+            if (side == 0 && lane == 0) norm0[static_cast<size_t>(b) * N0pad + row] = n;
+            wmax = fmaxf(wmax, n);
+        }
     }
     __shared__ float smax[8];
     if (lane == 0) smax[warp] = wmax;

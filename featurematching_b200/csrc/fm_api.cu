@@ -145,7 +145,7 @@ CoarseWorkspace coarse_workspace(const CoarseDims& d, bool fp32_input, void* bas
     w.l2col = reinterpret_cast<float*>(take(sizeof(float) * (B * d.N1 + kBlockN)));   // slack: the exact pass reads whole blocks
     w.rowslot = reinterpret_cast<int2*>(take(sizeof(int2) * B * d.N0 * kRowSlots));
     w.tie_list = reinterpret_cast<int4*>(take(sizeof(int4) * kTieCap));
-    w.blocksum = reinterpret_cast<int*>(take(sizeof(int) * ((B * d.N0 + 1023) / 1024 + 1)));
+    w.blocksum = reinterpret_cast<int*>(take(sizeof(int) * kMaxResolveBlocks));
     w.hot_meta = reinterpret_cast<uint2*>(take(sizeof(uint2) * static_cast<size_t>(d.num_pools) * d.hot_cap));
     w.hot_dots = reinterpret_cast<float*>(take(sizeof(float) * kHotChunk * static_cast<size_t>(d.num_pools) * d.hot_cap));
     if (fp32_input) {

@@ -53,6 +53,8 @@ struct CoarseDims {
 // the confidence threshold.  K1 stores the raw dot products; K2 evaluates all 32 exactly.
 constexpr int kHotChunk = 32;
 
+constexpr int kMaxResolveBlocks = 4096;   // grid bound of the cooperative resolve kernel (co-resident blocks)
+
 struct CoarseWorkspace {
     // all pointers into the caller's workspace
     __nv_bfloat16* f0b;   // [B, N0, C] bf16 copy (only if the input was fp32)
@@ -73,7 +75,7 @@ struct CoarseWorkspace {
     int* tie_count;       // entries in tie_list (may exceed kTieCap: then FM_FLAG_TIE_OVERFLOW)
     int4* tie_list;       // [kTieCap] (row, j, conf bits, 0): matches beyond a row's kRowSlots
     int* redo;            // 1 = the single-pass candidate filter overflowed: re-extract with exact row sums
-    int* blocksum;        // [ceil(B * N0 / 1024)] + scanned copy
+    int* blocksum;        // [kMaxResolveBlocks] per-block match counts of the resolve kernel
     size_t zero_begin, zero_bytes;   // region cleared at the start of every call
     size_t total_bytes;
 };
