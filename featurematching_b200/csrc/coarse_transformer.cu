@@ -626,7 +626,7 @@ cudaError_t launch_coarse_transformer(const float* feat0, const float* feat1, in
     float* ksum = reinterpret_cast<float*>(ws + pl.ksum);
     cudaError_t e;
 
-    for (int l = 0; l < n_layers; ++l) {
+    for (int l = 0; layer_params && l < n_layers; ++l) {   // NULL: packed by an earlier call into this workspace
         CtLayerParams lp;
         const void* const* src = layer_params + static_cast<size_t>(l) * 10;
         lp.q = static_cast<const float*>(src[0]); lp.k = static_cast<const float*>(src[1]);

@@ -564,7 +564,7 @@ cudaError_t launch_fine_transformer(const float* win0, const float* win1, const 
                                     int n_layers, const int* kinds, const float* const* layer_ptrs, float* out0,
                                     float* out1, void* workspace, int num_sms, cudaStream_t st) {
     uint8_t* blobs = static_cast<uint8_t*>(workspace);
-    for (int l = 0; l < n_layers; ++l) {
+    for (int l = 0; layer_ptrs && l < n_layers; ++l) {   // NULL: packed by an earlier call into this workspace
         const float* const* q = layer_ptrs + 10 * l;
         TfLayerParams lp{q[0], q[1], q[2], q[3], q[4], q[5], q[6], q[7], q[8], q[9]};
         tf_pack_kernel<<<20, 256, 0, st>>>(lp, blobs + static_cast<size_t>(l) * kBlobBytes); count_launch();

@@ -474,7 +474,7 @@ size_t fm_fine_transformer_workspace_bytes(int n_layers) {
 int fm_fine_transformer(const float* win0, const float* win1, const int32_t* count, int capacity, int WW, int C,
                         int nhead, int n_layers, const int32_t* layer_kinds, const float* const* layer_params,
                         float* out0, float* out1, void* workspace, size_t workspace_bytes, void* stream) {
-    if (!win0 || !win1 || !out0 || !out1 || !layer_kinds || !layer_params || !workspace) { set_error("null pointer argument"); return FM_ERR_BAD_ARG; }
+    if (!win0 || !win1 || !out0 || !out1 || !layer_kinds || !workspace) { set_error("null pointer argument"); return FM_ERR_BAD_ARG; }
     if (n_layers < 1 || n_layers > 16 || capacity < 0) { set_error("n_layers must be in [1, 16] and capacity >= 0"); return FM_ERR_BAD_ARG; }
     if (!fine_transformer_supported(C, nhead, WW)) {
         set_error("fine transformer supports d_model 64, nhead 8, WW <= 49 (got C=%d nhead=%d WW=%d)", C, nhead, WW);
@@ -482,7 +482,7 @@ int fm_fine_transformer(const float* win0, const float* win1, const int32_t* cou
     }
     for (int l = 0; l < n_layers; ++l) {
         if (layer_kinds[l] != 0 && layer_kinds[l] != 1) { set_error("layer_kinds[%d] must be 0 (self) or 1 (cross)", l); return FM_ERR_BAD_ARG; }
-        for (int k = 0; k < 10; ++k)
+        for (int k = 0; layer_params && k < 10; ++k)   // layer_params == NULL: the workspace holds them packed already
             if (!layer_params[10 * l + k]) { set_error("layer_params[%d] is NULL", 10 * l + k); return FM_ERR_BAD_ARG; }
     }
     if ((reinterpret_cast<uintptr_t>(win0) | reinterpret_cast<uintptr_t>(win1) | reinterpret_cast<uintptr_t>(out0) |
@@ -512,7 +512,7 @@ int fm_coarse_transformer(const float* feat0, const float* feat1, int B, int L0,
                           int n_layers, const int32_t* layer_kinds, const float* const* layer_params, float* out0,
                           float* out1, void* out0_bf16, void* out1_bf16, void* workspace, size_t workspace_bytes,
                           void* stream) {
-    if (!layer_kinds || !layer_params || !workspace) { set_error("null pointer argument"); return FM_ERR_BAD_ARG; }
+    if (!layer_kinds || !workspace) { set_error("null pointer argument"); return FM_ERR_BAD_ARG; }
     if (n_layers < 1 || n_layers > 32 || B < 0 || L0 < 0 || L1 < 0) { set_error("n_layers must be in [1, 32] and B, L0, L1 >= 0"); return FM_ERR_BAD_ARG; }
     if ((static_cast<size_t>(B) * L0 && (!feat0 || !out0)) || (static_cast<size_t>(B) * L1 && (!feat1 || !out1))) {
         set_error("null token pointer");
@@ -524,7 +524,7 @@ int fm_coarse_transformer(const float* feat0, const float* feat1, int B, int L0,
     }
     for (int l = 0; l < n_layers; ++l) {
         if (layer_kinds[l] != 0 && layer_kinds[l] != 1) { set_error("layer_kinds[%d] must be 0 (self) or 1 (cross)", l); return FM_ERR_BAD_ARG; }
-        for (int k = 0; k < 10; ++k)
+        for (int k = 0; layer_params && k < 10; ++k)   // layer_params == NULL: the workspace holds them packed already
             if (!layer_params[10 * l + k]) { set_error("layer_params[%d] is NULL", 10 * l + k); return FM_ERR_BAD_ARG; }
     }
     if ((reinterpret_cast<uintptr_t>(feat0) | reinterpret_cast<uintptr_t>(feat1) | reinterpret_cast<uintptr_t>(out0) |

@@ -211,9 +211,57 @@ __device__ __forceinline__ int block_sum_int(int v, int* scratch) {
     return s;
 }
 
+// Cyclic Jacobi of a symmetric 9 x 9 matrix by ONE WARP (a, v in shared memory, doubles): the same rotations in the
+// same order as pose::jacobi_eigen, with the nine elements of each row / column update on nine lanes.  (Run by a
+// single thread the eight refits of a polish took 22 ms per 32 pairs: ~100 k dependent fp64 operations each.)
+__device__ void jacobi9_warp(double* a, double* v, int lane) {
+    if (lane < 9)
+        for (int j = 0; j < 9; ++j) v[lane * 9 + j] = lane == j ? 1.0 : 0.0;
+    __syncwarp();
+    for (int sweep = 0; sweep < 30; ++sweep) {
+        double off = 0.0, dg = 0.0;
+        if (lane < 9)
+            for (int q = 0; q < 9; ++q) {
+                const double x = a[lane * 9 + q];
+                if (q == lane) dg = x * x; else off += x * x;
+            }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            off += __shfl_xor_sync(0xffffffffu, off, o);
+            dg += __shfl_xor_sync(0xffffffffu, dg, o);
+        }
+        if (off * 0.5 <= dg * 1e-30) break;   // warp-uniform
+        for (int p = 0; p < 9; ++p)
+            for (int q = p + 1; q < 9; ++q) {
+                const double apq = a[p * 9 + q], app = a[p * 9 + p], aqq = a[q * 9 + q];
+                __syncwarp();                  // everyone holds the pivot entries before anyone rewrites them
+                if (apq == 0.0) continue;      // warp-uniform
+                const double theta = (aqq - app) / (2.0 * apq);
+                const double tt = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+                const double c = 1.0 / sqrt(tt * tt + 1.0), sn = tt * c;
+                if (lane < 9) {                // A <- A J (columns p, q): lane = row
+                    const double akp = a[lane * 9 + p], akq = a[lane * 9 + q];
+                    a[lane * 9 + p] = c * akp - sn * akq;
+                    a[lane * 9 + q] = sn * akp + c * akq;
+                }
+                __syncwarp();
+                if (lane < 9) {                // A <- J' A (rows p, q): lane = column; V <- V J
+                    const double apk = a[p * 9 + lane], aqk = a[q * 9 + lane];
+                    a[p * 9 + lane] = c * apk - sn * aqk;
+                    a[q * 9 + lane] = sn * apk + c * aqk;
+                    const double vkp = v[lane * 9 + p], vkq = v[lane * 9 + q];
+                    v[lane * 9 + p] = c * vkp - sn * vkq;
+                    v[lane * 9 + q] = sn * vkp + c * vkq;
+                }
+                __syncwarp();
+            }
+    }
+}
+
 // ---- 5. one CTA = one start of one pair: local optimisation
 __global__ void __launch_bounds__(kPoseThreads) pose_polish_kernel(PoseParams p, PoseWs w) {
     __shared__ double s_ata[kPoseThreads / 32][45];
+    __shared__ double s_A[81], s_V[81];
     __shared__ float s_E[9];
     __shared__ double s_Ed[9];
     __shared__ float s_red[kPoseThreads / 32];
@@ -272,24 +320,24 @@ __global__ void __launch_bounds__(kPoseThreads) pose_polish_kernel(PoseParams p,
                 if (lane == 0) s_ata[warp][i] = v;
             }
             __syncthreads();
-            if (threadIdx.x == 0) {
-                double ata[81], vec[81];
-                int k = 0;
-                for (int i = 0; i < 9; ++i)
-                    for (int j = i; j < 9; ++j) {
-                        double v = 0.0;
-                        for (int ww = 0; ww < kPoseThreads / 32; ++ww) v += s_ata[ww][k];
-                        ata[i * 9 + j] = v;
-                        ata[j * 9 + i] = v;
-                        ++k;
-                    }
-                jacobi_eigen<double, 9>(ata, vec, 30);
-                int kmin = 0;
-                for (int i = 1; i < 9; ++i) if (ata[i * 10] < ata[kmin * 10]) kmin = i;
-                double Er[9];
-                for (int i = 0; i < 9; ++i) Er[i] = vec[i * 9 + kmin];
-                project_essential(Er);
-                for (int i = 0; i < 9; ++i) { s_Ed[i] = Er[i]; s_E[i] = static_cast<float>(Er[i]); }
+            if (warp == 0) {
+                for (int e = lane; e < 81; e += 32) {          // the full symmetric matrix from the warps' packed partials
+                    const int r = e / 9, c = e - r * 9, i = min(r, c), j = max(r, c);
+                    const int k = i * 9 - (i * (i - 1)) / 2 + (j - i);
+                    double v = 0.0;
+                    for (int ww = 0; ww < kPoseThreads / 32; ++ww) v += s_ata[ww][k];
+                    s_A[e] = v;
+                }
+                __syncwarp();
+                jacobi9_warp(s_A, s_V, lane);
+                if (lane == 0) {
+                    int kmin = 0;
+                    for (int i = 1; i < 9; ++i) if (s_A[i * 10] < s_A[kmin * 10]) kmin = i;
+                    double Er[9];
+                    for (int i = 0; i < 9; ++i) Er[i] = s_V[i * 9 + kmin];
+                    project_essential(Er);
+                    for (int i = 0; i < 9; ++i) { s_Ed[i] = Er[i]; s_E[i] = static_cast<float>(Er[i]); }
+                }
             }
             __syncthreads();
             float Ef[9];

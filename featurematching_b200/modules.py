@@ -409,10 +409,26 @@ class LocalFeatureTransformer(nn.Module):
             if p.dim() > 1:
                 nn.init.xavier_uniform_(p)
 
+    def _layer_args(self, dev, ws):
+        """(n, kinds, ptrs, keepalive): ctypes arguments of the layers' parameters.  `ptrs` is None when `ws` (the
+        workspace tensor) already holds these very parameters in packed form: same workspace storage, same
+        parameter storages and versions as the previous call -- the eval-mode case, where re-packing 0.65 M weights
+        per layer on every call is wasted work."""
+        import ctypes
+        n = len(self.layers)
+        params = [t.detach().to(device=dev, dtype=torch.float32).contiguous()
+                  for layer in self.layers for t in layer.flat_parameters()]
+        key = (ws.data_ptr(), tuple((t.data_ptr(), t._version) for layer in self.layers for t in layer.flat_parameters()),
+               tuple(t.data_ptr() for t in params))
+        kinds = (ctypes.c_int32 * n)(*[0 if k == 'self' else 1 for k in self.layer_names])
+        if getattr(self, "_packed_key", None) == key:
+            return n, kinds, None, params
+        self._packed_key = key
+        return n, kinds, (ctypes.c_void_p * (10 * n))(*[t.data_ptr() for t in params]), params
+
     def transform(self, feat0, feat1, count=None, out=None):
         """Device-side call: [cap, WW, C] fp32 windows -> updated windows (`out` may be the
         inputs themselves); `count` = device int32 match count for padded buffers."""
-        import ctypes
         lib = _lib.load()
         _require_cuda(feat0, feat1)
         f0 = feat0.to(torch.float32).contiguous()
@@ -422,29 +438,18 @@ class LocalFeatureTransformer(nn.Module):
         o0, o1 = out if out is not None else (torch.empty_like(f0), torch.empty_like(f1))
         if cap == 0:
             return o0, o1
-        n = len(self.layers)
-        params = [t.detach().to(device=dev, dtype=torch.float32).contiguous()
-                  for layer in self.layers for t in layer.flat_parameters()]
-        kinds = (ctypes.c_int32 * n)(*[0 if k == 'self' else 1 for k in self.layer_names])
-        ptrs = (ctypes.c_void_p * (10 * n))(*[t.data_ptr() for t in params])
-        nbytes = lib.fm_fine_transformer_workspace_bytes(n)
+        nbytes = lib.fm_fine_transformer_workspace_bytes(len(self.layers))
         ws = self._ws.get(nbytes, dev)
+        n, kinds, ptrs, params = self._layer_args(dev, ws)
         with torch.cuda.device(dev):
             rc = lib.fm_fine_transformer(_lib.ptr(f0), _lib.ptr(f1), _lib.ptr(count), cap, WW, C,
                                          self.nhead, n, kinds, ptrs, _lib.ptr(o0), _lib.ptr(o1),
                                          _lib.ptr(ws), nbytes, _lib.stream_ptr(dev))
+        if rc != 0:
+            self._packed_key = None
         _lib.check(rc, "fm_fine_transformer")
         self._keepalive = params   # the launch is asynchronous
         return o0, o1
-
-    def _packed_args(self, dev):
-        import ctypes
-        n = len(self.layers)
-        params = [t.detach().to(device=dev, dtype=torch.float32).contiguous()
-                  for layer in self.layers for t in layer.flat_parameters()]
-        kinds = (ctypes.c_int32 * n)(*[0 if k == 'self' else 1 for k in self.layer_names])
-        ptrs = (ctypes.c_void_p * (10 * n))(*[t.data_ptr() for t in params])
-        return n, params, kinds, ptrs
 
     def transform_tokens(self, feat0, feat1, out=None, bf16_out=None):
         """Coarse call (d_model 256): [B, L0, C], [B, L1, C] fp32 tokens -> updated tokens.  `bf16_out` =
@@ -461,13 +466,15 @@ class LocalFeatureTransformer(nn.Module):
         dev = f0.device
         o0, o1 = out if out is not None else (torch.empty_like(f0), torch.empty_like(f1))
         b0, b1 = bf16_out if bf16_out is not None else (None, None)
-        n, params, kinds, ptrs = self._packed_args(dev)
-        nbytes = lib.fm_coarse_transformer_workspace_bytes(B, L0, L1, n)
+        nbytes = lib.fm_coarse_transformer_workspace_bytes(B, L0, L1, len(self.layers))
         ws = self._ws.get(max(nbytes, 256), dev)
+        n, kinds, ptrs, params = self._layer_args(dev, ws)
         with torch.cuda.device(dev):
             rc = lib.fm_coarse_transformer(_lib.ptr(f0), _lib.ptr(f1), B, L0, L1, C, self.nhead, n, kinds, ptrs,
                                            _lib.ptr(o0), _lib.ptr(o1), _lib.ptr(b0), _lib.ptr(b1),
                                            _lib.ptr(ws), nbytes, _lib.stream_ptr(dev))
+        if rc != 0:
+            self._packed_key = None
         _lib.check(rc, "fm_coarse_transformer")
         self._keepalive = params   # the launch is asynchronous
         return o0, o1

@@ -179,6 +179,10 @@ FM_API int fm_fine_match(const void* win0, const void* win1, int win_dtype, cons
  * workspace must be 32-byte aligned (256-bit global accesses).
  * All GEMMs run on the tensor cores with fp32-grade 3-term bf16 splits; entries >= *count are
  * not touched. */
+/* Both transformers: the first bytes of `workspace` receive the layers' weights in operand form (bf16 hi + lo planes,
+ * pre-swizzled).  `layer_params` == NULL skips that packing: the workspace must then be the one (same pointer, same
+ * n_layers) an earlier call with the same parameters packed -- what a module does in eval mode, where the weights do
+ * not change between calls (network/module/transformer.py:59-97 holds them as nn.Parameters). */
 FM_API size_t fm_fine_transformer_workspace_bytes(int n_layers);
 FM_API int fm_fine_transformer(const float* win0, const float* win1, const int32_t* count, int capacity,
                         int WW, int C, int nhead, int n_layers, const int32_t* layer_kinds,

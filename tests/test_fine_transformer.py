@@ -248,3 +248,30 @@ def test_chain_with_transformer_kernels_match_reference_golden(golden_dir):
     fin(w0, w1, data)
     torch.cuda.synchronize()
     compare.check_fine(data["mkpts0_f"], data["mkpts1_f"], want["mkpts0_f"], want["mkpts1_f"])
+
+
+@pytest.mark.gpu
+def test_packed_weights_are_reused_and_invalidated():
+    """Eval-mode calls reuse the weights packed into the module's workspace (layer_params = NULL through the C ABI);
+    an in-place parameter update or a new workspace forces a re-pack."""
+    import torch
+    from featurematching_b200 import modules
+    from oracle import matcher_oracle as mo
+    torch.manual_seed(3)
+    names = ["self", "cross"]
+    m = modules.LocalFeatureTransformer({"d_model": 64, "nhead": 8, "layer_names": names, "attention": "linear"}).eval().cuda()
+    x0, x1 = torch.randn(37, 49, 64), torch.randn(37, 49, 64)
+    a0, a1 = m(x0.cuda(), x1.cuda())
+    assert m._packed_key is not None
+    key = m._packed_key
+    b0, b1 = m(x0.cuda(), x1.cuda())             # second call: packing skipped
+    assert m._packed_key == key
+    assert torch.equal(a0, b0) and torch.equal(a1, b1)
+    with torch.no_grad():
+        m.layers[0].q_proj.weight.mul_(0.5)      # in-place update bumps the version: must re-pack
+    c0, c1 = m(x0.cuda(), x1.cuda())
+    assert m._packed_key != key
+    layers = mo.transformer_params_from_state_dict({k: v.cpu() for k, v in m.state_dict().items()}, len(names))
+    r0, r1 = mo.local_feature_transformer(x0, x1, layers, names, 8)
+    assert (c0.cpu() - r0).abs().max() < 2e-4 and (c1.cpu() - r1).abs().max() < 2e-4
+    assert (c0 - a0).abs().max() > 1e-3          # and the result did change
