@@ -296,54 +296,74 @@ class OverlappedGather:
             coarse stage of this batch             # the persistent 148-CTA kernel keeps every SM to itself
             g.launch()                             # exchange of the PREVIOUS batch starts here, behind it
             gather / fine transformer / fine match
-            g.before_pack()                        # the records buffer is free again (device-side wait)
             pack records into r.records
-            g.stage(r.records, r.capacity)         # marks them ready; nothing is sent yet
+            g.stage(r.records, r.capacity)         # copies them into one of two staging slots; nothing is sent yet
         out = g.finish()                           # sends the last batch, joins the side stream
 
-    No host synchronisation anywhere; `out` (on the consumer rank, None elsewhere when dst is set) is valid once
-    the current stream has passed finish() / the next before_pack()."""
+    No host synchronisation anywhere; `out` (on the consumer rank, None elsewhere when dst is set) belongs to the
+    most recent exchange and is valid once the current stream has passed finish()."""
 
     def __init__(self, device, group=None, dst=None):
         self.device = torch.device(device)
         self.group, self.dst = group, dst
         self.side = torch.cuda.Stream(device=self.device)
-        self.packed = torch.cuda.Event()
+        # two staging slots: stage() copies the caller's records (a few MB, device to device), so the caller's
+        # buffer is free at once and an exchange has TWO steps to complete before its slot is needed again -- with
+        # one buffer the pack of step k + 1 waited for exchange k, and a send cannot finish before the consumer
+        # rank has posted the matching receive: the ranks ran in lockstep plus skew (r02: 8.8 vs 7.0 ms per step
+        # on the sending rank of a 2-rank sequence job)
+        self.slots = [None, None]
+        self.packed = [torch.cuda.Event(), torch.cuda.Event()]
+        self.done = [torch.cuda.Event(), torch.cuda.Event()]
+        self.busy = [False, False]
         self.gate = torch.cuda.Event()
-        self.done = torch.cuda.Event()
+        self.turn = 0
         self.staged = None
-        self.pending = False
         self.out = None
 
     def stage(self, records, capacity):
-        self.packed.record(torch.cuda.current_stream(self.device))
-        self.staged = (records, capacity)
+        n = (capacity + 1) * _lib.RECORD_BYTES
+        s = self.turn
+        self.turn ^= 1
+        cur = torch.cuda.current_stream(self.device)
+        if self.busy[s]:
+            cur.wait_event(self.done[s])      # the exchange that used this slot two steps ago
+            self.busy[s] = False
+        if self.slots[s] is None or self.slots[s].numel() != n:
+            self.slots[s] = torch.empty(n, dtype=torch.uint8, device=self.device)
+        self.slots[s].copy_(records[:n], non_blocking=True)
+        self.packed[s].record(cur)
+        if self.staged is not None:           # stage() twice without launch(): send the older one now
+            self.launch()
+        self.staged = (s, capacity)
 
     def launch(self):
         if self.staged is None:
             return self.out
-        records, capacity = self.staged
+        s, capacity = self.staged
         self.staged = None
         self.gate.record(torch.cuda.current_stream(self.device))   # behind whatever the caller enqueued so far
-        self.side.wait_event(self.packed)
+        self.side.wait_event(self.packed[s])
         self.side.wait_event(self.gate)
         with torch.cuda.stream(self.side):
-            self.out = gather_matches(records, capacity, self.group, self.dst)
-            self.done.record(self.side)
-        self.pending = True
+            self.out = gather_matches(self.slots[s], capacity, self.group, self.dst)
+            self.done[s].record(self.side)
+        self.busy[s] = True
         return self.out
 
     def before_pack(self):
+        """Kept for callers written against the single-buffer version: the caller's records buffer is never
+        held by an exchange any more, so this only makes sure a staged exchange has been enqueued."""
         self.launch()
-        if self.pending:
-            torch.cuda.current_stream(self.device).wait_event(self.done)
 
     def finish(self):
         """Sends what is staged and joins the side stream into the current one (device-side)."""
         self.launch()
-        if self.pending:
-            torch.cuda.current_stream(self.device).wait_event(self.done)
-            self.pending = False
+        cur = torch.cuda.current_stream(self.device)
+        for s in range(2):
+            if self.busy[s]:
+                cur.wait_event(self.done[s])
+                self.busy[s] = False
         return self.out
 
 
