@@ -74,6 +74,9 @@ def parse_args():
                          "beside the step and reported under kernels.fine_transformer with in_step = false")
     ap.add_argument("--with-fine-transformer", action="store_true", help="(default since round 2; kept for old command lines)")
     ap.add_argument("--frames", type=int, default=10000, help="--config seq10k: frames of the sequence")
+    ap.add_argument("--seed-rank", type=int, default=None, help=argparse.SUPPRESS)
+    ap.add_argument("--exchange-every", type=int, default=8,
+                    help="--config seq10k: steps whose records are exchanged together (one exchange per E steps)")
     ap.add_argument("--gather", default="root", choices=["root", "all"],
                     help="N > 1: match records go to rank 0 only (grouped send/recv) or to every rank (all_gather)")
     ap.add_argument("--no-gpu-eager-baseline", action="store_true")
@@ -453,7 +456,7 @@ def init_gpu(args):
     return rank, world, local, dev
 
 
-def step_loop(args, head, ftm, og, lib, rank, B, inputs, shapes_, K, stage_events=True, pair_offset=None):
+def step_loop(args, head, ftm, og, lib, rank, B, inputs, shapes_, K, stage_events=True, pair_offset=None, group=None):
     """K steps of the head on `inputs` (a function k -> (fc0, fc1, ff0, ff1)), the same kernel sequence as
     MatchHead.run with stage boundaries marked by CUDA events.  Returns (result, per-step event rows)."""
     import torch
@@ -487,12 +490,23 @@ def step_loop(args, head, ftm, og, lib, rank, B, inputs, shapes_, K, stage_event
         if og:
             og.before_pack()
         off = rank * B if pair_offset is None else pair_offset(k)
-        rc = lib.fm_pack_matches(_lib.ptr(c.b_ids), _lib.ptr(c.i_ids), _lib.ptr(c.j_ids), _lib.ptr(c.mconf),
-                                 _lib.ptr(r.mkpts0_f), _lib.ptr(r.mkpts1_f), _lib.ptr(c.status), r.capacity,
-                                 off, _lib.ptr(r.records), _lib.stream_ptr(dev))
-        _lib.check(rc, "fm_pack_matches")
-        if og:
-            og.stage(r.records, r.capacity)
+        if group is not None:
+            # the sequence job exchanges every E steps: E steps' records land behind one another in one buffer
+            # (fm_pack_matches_append), which is staged for the exchange when the group is complete
+            E, big, counts, ci, last = group["every"], group["records"], group["counts"], group["index"], group["last"]
+            rc = lib.fm_pack_matches_append(_lib.ptr(c.b_ids), _lib.ptr(c.i_ids), _lib.ptr(c.j_ids), _lib.ptr(c.mconf),
+                                            _lib.ptr(r.mkpts0_f), _lib.ptr(r.mkpts1_f), _lib.ptr(c.status), r.capacity,
+                                            off, _lib.ptr(counts), ci, E * r.capacity, _lib.ptr(big), _lib.stream_ptr(dev))
+            _lib.check(rc, "fm_pack_matches_append")
+            if og and (ci == E - 1 or last):
+                og.stage(big, E * r.capacity)
+        else:
+            rc = lib.fm_pack_matches(_lib.ptr(c.b_ids), _lib.ptr(c.i_ids), _lib.ptr(c.j_ids), _lib.ptr(c.mconf),
+                                     _lib.ptr(r.mkpts0_f), _lib.ptr(r.mkpts1_f), _lib.ptr(c.status), r.capacity,
+                                     off, _lib.ptr(r.records), _lib.stream_ptr(dev))
+            _lib.check(rc, "fm_pack_matches")
+            if og:
+                og.stage(r.records, r.capacity)
         if e:
             e[5].record()
             rows.append(e)
@@ -792,11 +806,12 @@ def run_job(args):
     n_pairs, n_frames = end - begin, f_hi - f_lo
     # this rank's frames (synthetic: every rank's block is its own planted chain; a real loader would read frames
     # f_lo .. f_hi - 1), generated in chunks to bound the fp32 transients
+    srank = rank if args.seed_rank is None else args.seed_rank   # (debug) another rank's synthetic block
     toks, maps = [], []
     for c0 in range(0, n_frames, 512):
         c1 = min(c0 + 512 + 1, n_frames)   # one frame of overlap keeps the chain continuous across chunks
-        F, _ = synth.sequence_features(c1 - c0, N, 256, args.noise, 1234 + 7919 * rank + c0, device=dev)
-        G, _ = synth.fine_features(c1 - c0, 64, hw_f[0], hw_f[1], 4321 + 7919 * rank + c0, device=dev)
+        F, _ = synth.sequence_features(c1 - c0, N, 256, args.noise, 1234 + 7919 * srank + c0, device=dev)
+        G, _ = synth.fine_features(c1 - c0, 64, hw_f[0], hw_f[1], 4321 + 7919 * srank + c0, device=dev)
         last = c1 == n_frames
         toks.append(F if last else F[:-1]); maps.append(G if last else G[:-1])
         if last:
@@ -815,36 +830,55 @@ def run_job(args):
         return frames[lo:hi], frames[lo + 1:hi + 1], fmaps[lo:hi], fmaps[lo + 1:hi + 1]
 
     shp = (hw_i, hw_c, hw_f)
+    E = max(1, min(args.exchange_every, 64))
+    cap = head.default_capacity(B, hw_c, hw_c, head.coarse_matching.border_rm)
+    grp = {"every": E, "records": torch.zeros((E * cap + 1) * _lib.RECORD_BYTES, dtype=torch.uint8, device=dev),
+           "counts": torch.zeros(_lib.MAX_CHUNKS, dtype=torch.int32, device=dev)}
     step_loop(args, head, ftm, og, lib, rank, B, inputs, shp, min(max(args.warmup, 3), steps), stage_events=False)
     if og:
+        # warm-up of the exchange itself, at the timed region's message size and through BOTH staging slots: NCCL
+        # connects peers (and sizes its buffers) lazily at the first send / receive -- ~150 ms once, which at
+        # N > 1 otherwise lands inside a job that takes 300-700 ms in all
+        og.finish()
+        for _ in range(2):
+            og.stage(grp["records"], E * cap)
+            og.launch()
         og.finish()
     torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
-        sampler.start()
+        sampler.start()   # BEFORE the barrier: it sleeps 150 ms, and a rank that enters the job late makes every
+                          # other rank wait at its first exchange (r02: the whole "rank 1 is 27 % slower" mystery)
+    if world > 1:
+        dist.barrier()
     counts = torch.zeros(steps, dtype=torch.int32, device=dev)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     launches0 = lib.fm_launch_count()
     torch.cuda.synchronize()
     t_host0 = time.perf_counter()
     ev[0].record()
+    step_ev = [] if os.environ.get("FM_BENCH_STEP_TRACE") else None   # (debug) per-step device times of every rank
     for k in range(steps):
+        grp["index"], grp["last"] = k % E, k == steps - 1
         r, _ = step_loop(args, head, ftm, og, lib, rank, B, lambda _k, kk=k: inputs(kk), shp, 1, stage_events=False,
-                         pair_offset=lambda _k, kk=k: begin + kk * B)
+                         pair_offset=lambda _k, kk=k: begin + kk * B, group=grp)
         counts[k:k + 1].copy_(r.coarse.status[:1], non_blocking=True)   # device-side bookkeeping, no sync
+        if step_ev is not None:
+            step_ev.append(torch.cuda.Event(enable_timing=True)); step_ev[-1].record()
     if og:
         og.finish()
     ev[1].record()
     host_ms = (time.perf_counter() - t_host0) * 1e3   # host-side enqueue time of the whole job (no sync inside)
     torch.cuda.synchronize()
+    if step_ev:
+        ts = [ev[0].elapsed_time(e) for e in step_ev]
+        sys.stderr.write(f"rank {rank} step ms: " + " ".join(f"{b - a:.2f}" for a, b in zip([0.0] + ts[:-1], ts)) + "\n")
     ms = ev[0].elapsed_time(ev[1])
     launches = lib.fm_launch_count() - launches0
-    per_rank = [[ms, host_ms]]
+    per_rank = [[ms, host_ms, float(counts.sum().item())]]
     if world > 1:
-        allr = torch.zeros(world, 2, device=dev)
-        allr[rank, 0], allr[rank, 1] = ms, host_ms
+        allr = torch.zeros(world, 3, device=dev)
+        allr[rank, 0], allr[rank, 1], allr[rank, 2] = ms, host_ms, float(counts.sum().item())
         dist.all_reduce(allr)
         per_rank = allr.tolist()
         ms = max(r[0] for r in per_rank)
@@ -865,12 +899,13 @@ def run_job(args):
                 "config": {"workload": f"{CONFIGS[args.config]['name']}: {args.frames} frames -> {total_pairs} consecutive pairs, "
                                        f"block-sharded over {world} rank(s) with a one-frame halo (pipeline.shard_sequence), "
                                        f"{B} pairs per step per rank" + (", fine transformer in the step" if args.with_fine_transformer else "")
-                                       + (", records to rank 0 behind each step" if world > 1 else ""),
+                                       + (f", records to rank 0 every {E} steps" if world > 1 else ""),
                            "N0": N, "N1": N, "C": 256, "fine_map": [64, hw_f[0], hw_f[1]], "pairs_rank0": n_pairs,
                            "matches_total": int(matches[0]), "l2": "every step reads new frames (no reuse between steps)"},
                 "gpu_launches": int(launches), "clocks": clocks,
                 "per_rank_ms": [round(r[0], 2) for r in per_rank],
-                "per_rank_host_enqueue_ms": [round(r[1], 2) for r in per_rank]}
+                "per_rank_host_enqueue_ms": [round(r[1], 2) for r in per_rank],
+                "per_rank_matches": [int(r[2]) for r in per_rank]}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
