@@ -191,7 +191,7 @@ class MatchHead:
         return st
 
     def match_host(self, feat_c0, feat_c1, feat_f0, feat_f1, hw0_i, hw0_c, hw1_c, hw0_f, pair_offset=0,
-                   chunks=8):
+                   chunks=16):
         """End-to-end call on HOST tensors (pinned for full copy bandwidth).  The batch is cut into
         `chunks` groups of pairs; group k + 1 crosses PCIe on a copy stream while group k runs the
         head; the groups' packed records are appended on the device (fm_pack_matches_append) and
