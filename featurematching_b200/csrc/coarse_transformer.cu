@@ -5,8 +5,8 @@
 // 'self' / 'cross' (shipped: ['self', 'cross'] * 4).
 //
 // The layer is five token-parallel GEMMs around one cross-token reduction (the per-image, per-head
-// 32 x 32 matrices KV = K'^T V of the linear attention).  All five GEMMs run in ONE persistent
-// tcgen05 kernel template (ct_gemm_kernel) that differs only in its epilogue:
+// 32 x 32 matrices KV = K'^T V of the linear attention).  All GEMMs (six with the block-diagonal message product)
+// run in ONE persistent tcgen05 kernel template (ct_gemm_kernel) that differs only in its epilogue:
 //
 //   half-pass (x rows of one image side, source rows of the same or the other side)
 //     1. KV   : source . [Wk; Wv]^T       -> K' = elu + 1, V / S (fp32)          epilogue kEpiKV
@@ -25,12 +25,16 @@
 // residual stream x).  The hi plane of the final x IS the bf16 feature tensor the coarse matcher
 // (K1) consumes -- there is no separate fp32 -> bf16 cast pass.
 //
-// GEMM kernel: tile 128 rows x 256 columns, K in blocks of 64; a stage = {A hi, A lo (16 KB each),
-// W hi, W lo (32 KB each)} = 96 KB, two stages; 12 MMAs (3 terms x 4 k-steps) per stage; two 256-column
-// TMEM accumulators so tile i's epilogue overlaps tile i+1's MMAs.  10 warps: TMA producer, MMA
-// issuer, 8 epilogue warps (2 per TMEM lane quarter, each owning 128 of the 256 columns; a thread
-// owns half a row).  A tile never straddles two images (3-D/4-D tensor maps with the image as its
-// own dimension; rows past L are zero-filled by TMA and never stored).
+// GEMM kernel: persistent CTA PAIRS (__cluster_dims__(2, 1, 1), tcgen05.mma.cta_group::2).  A pair owns a 256-row
+// x 256-column tile of one image; K in blocks of 64.  Each CTA TMA-loads its own 128 A rows and HALF of the W tile
+// (its 128 of the 256 output columns' rows): a stage = {A hi, A lo, W/2 hi, W/2 lo} = 4 x 16 KB = 64 KB per CTA,
+// three stages; both CTAs' loads complete on the leader's barrier; the leader's MMA thread issues 12 MMAs (3 terms
+// x 4 k-steps, M 256 N 256 K 16) per stage and frees the stage in both CTAs with a multicast commit.  Two 256-column
+// TMEM accumulators per CTA so tile i's epilogue overlaps tile i+1's MMAs.  10 warps per CTA: TMA producer, MMA
+// issuer (idle in the peer), 8 epilogue warps (2 per TMEM lane quarter, each owning 128 of the 256 columns; a
+// thread owns half a row of its CTA's 128 rows).  A tile never straddles two images (4-D tensor maps with the image
+// as its own dimension; rows past L -- including a pair's whole second half when an image has an odd number of
+// 128-row tiles -- are zero-filled by TMA and never stored).  tools/probe_2cta.cu pins the operand split.
 #include <cuda.h>
 
 #include <algorithm>
