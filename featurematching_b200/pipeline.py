@@ -190,15 +190,12 @@ class MatchHead:
         self._host["state"] = st
         return st
 
-    def match_host(self, feat_c0, feat_c1, feat_f0, feat_f1, hw0_i, hw0_c, hw1_c, hw0_f, pair_offset=0,
-                   chunks=16):
-        """End-to-end call on HOST tensors (pinned for full copy bandwidth).  The batch is cut into
-        `chunks` groups of pairs; group k + 1 crosses PCIe on a copy stream while group k runs the
-        head; the groups' packed records are appended on the device (fm_pack_matches_append) and
-        come back, with the status words, in asynchronous copies.  One host synchronisation per
-        call.  Returns (records as a numpy structured array (RECORD_DTYPE) that VIEWS a pinned
-        landing buffer reused by the next call -- copy it to keep it --, bytes host->device, bytes
-        device->host)."""
+    def match_host_submit(self, feat_c0, feat_c1, feat_f0, feat_f1, hw0_i, hw0_c, hw1_c, hw0_f, pair_offset=0,
+                          chunks=16):
+        """First half of match_host: enqueues the H2D copies (copy stream), the head (current stream) and the D2H
+        copies of the records / status words, and returns a ticket WITHOUT synchronising.  Up to two tickets may
+        be outstanding (two pinned landing sets): submitting call k + 1 before collecting call k keeps the PCIe link
+        busy across calls -- call k + 1's first groups cross while call k's last group still runs."""
         import time
         t_start = time.perf_counter()
         B = feat_c0.shape[0]
@@ -212,23 +209,31 @@ class MatchHead:
         total_capacity = nch * capacity
         rec_bytes = (total_capacity + 1) * _lib.RECORD_BYTES
         land = self._host.get("land")
-        if land is None or land[0].numel() != rec_bytes or land[1].shape[0] != nch:
-            land = (torch.empty(rec_bytes, dtype=torch.uint8).pin_memory(),
-                    torch.empty(nch, _lib.STATUS_WORDS, dtype=torch.int32).pin_memory(),
-                    torch.empty(rec_bytes, dtype=torch.uint8, device=self.device),
-                    torch.zeros(_lib.MAX_CHUNKS, dtype=torch.int32, device=self.device))
+        if land is None or land["rec_bytes"] != rec_bytes or land["nch"] != nch:
+            land = {"rec_bytes": rec_bytes, "nch": nch, "turn": 0, "busy": [False, False],
+                    "host": [(torch.empty(rec_bytes, dtype=torch.uint8).pin_memory(),
+                              torch.empty(nch, _lib.STATUS_WORDS, dtype=torch.int32).pin_memory(),
+                              torch.cuda.Event()) for _ in range(2)],
+                    "rec_dev": torch.empty(rec_bytes, dtype=torch.uint8, device=self.device),
+                    "counts": torch.zeros(_lib.MAX_CHUNKS, dtype=torch.int32, device=self.device)}
             self._host["land"] = land
-        rec_host, status_host, rec_dev, counts_dev = land
+        idx = land["turn"]
+        if land["busy"][idx]:
+            raise _lib.FmError("match_host_submit: two calls are already outstanding; collect one with match_host_result")
+        land["turn"] ^= 1
+        land["busy"][idx] = True
+        rec_host, status_host, done = land["host"][idx]
+        rec_dev, counts_dev = land["rec_dev"], land["counts"]
         cur = torch.cuda.current_stream(self.device)
         cs = st["copy_stream"]
+        used = st.setdefault("used", [False, False])
         h2d = 0
-        cs.wait_stream(cur)   # staging buffers may still be read by the previous call's kernels
         for k in range(nch):
             lo, hi = k * chunk, min((k + 1) * chunk, B)
             slot = k & 1
             with torch.cuda.stream(cs):
-                if k >= 2:
-                    cs.wait_event(st["free"][slot])
+                if used[slot]:
+                    cs.wait_event(st["free"][slot])   # the group (of this or of the previous call) that read this slot
                 for d, t in zip(st["stage"][slot], ins):
                     d[:hi - lo].copy_(t[lo:hi], non_blocking=True)
                     h2d += (hi - lo) * t[0].numel() * t.element_size()
@@ -239,19 +244,45 @@ class MatchHead:
                          pack=False, append=(counts_dev, k, total_capacity, rec_dev))
             status_host[k].copy_(r.coarse.status, non_blocking=True)
             st["free"][slot].record(cur)
+            used[slot] = True
         rec_host.copy_(rec_dev, non_blocking=True)
-        t_enq = time.perf_counter()
-        cur.synchronize()
+        done.record(cur)
+        return {"idx": idx, "h2d": h2d, "d2h": rec_bytes + nch * _lib.STATUS_WORDS * 4, "t_start": t_start,
+                "t_enq": time.perf_counter()}
+
+    def match_host_result(self, ticket):
+        """Second half: waits for the ticket's device work (one host synchronisation on its event) and returns
+        (records, bytes host->device, bytes device->host) like match_host.  The records VIEW the ticket's pinned
+        landing buffer, which the call after next reuses -- copy them to keep them."""
+        import time
+        land = self._host["land"]
+        rec_host, status_host, done = land["host"][ticket["idx"]]
+        done.synchronize()
         t_sync = time.perf_counter()
+        land["busy"][ticket["idx"]] = False
         for k, stw in enumerate(status_host.tolist()):
             if stw[_lib.ST_FLAGS]:
                 raise _lib.FmError(f"coarse status flags {stw[_lib.ST_FLAGS]:#x} in chunk {k} (cand overflow=1, "
                                    f"output overflow=2, tie overflow=4, range=8); status={stw}")
         a = rec_host.numpy().view(RECORD_DTYPE)
-        rec = a[1:1 + int(a[0]["pair"])]   # a view of the pinned landing buffer: valid until the next call
+        rec = a[1:1 + int(a[0]["pair"])]
         # host-side split of the call (ms): enqueue, wait for the device, unpack
-        self.last_timing = ((t_enq - t_start) * 1e3, (t_sync - t_enq) * 1e3, (time.perf_counter() - t_sync) * 1e3)
-        return rec, h2d, rec_bytes + nch * _lib.STATUS_WORDS * 4
+        self.last_timing = ((ticket["t_enq"] - ticket["t_start"]) * 1e3, (t_sync - ticket["t_enq"]) * 1e3,
+                            (time.perf_counter() - t_sync) * 1e3)
+        return rec, ticket["h2d"], ticket["d2h"]
+
+    def match_host(self, feat_c0, feat_c1, feat_f0, feat_f1, hw0_i, hw0_c, hw1_c, hw0_f, pair_offset=0,
+                   chunks=16):
+        """End-to-end call on HOST tensors (pinned for full copy bandwidth).  The batch is cut into
+        `chunks` groups of pairs; group k + 1 crosses PCIe on a copy stream while group k runs the
+        head; the groups' packed records are appended on the device (fm_pack_matches_append) and
+        come back, with the status words, in asynchronous copies.  One host synchronisation per
+        call.  Returns (records as a numpy structured array (RECORD_DTYPE) that VIEWS a pinned
+        landing buffer reused by later calls -- copy it to keep it --, bytes host->device, bytes
+        device->host).  = match_host_result(match_host_submit(...)); a caller with a stream of batches
+        submits batch k + 1 before collecting batch k."""
+        return self.match_host_result(self.match_host_submit(feat_c0, feat_c1, feat_f0, feat_f1, hw0_i, hw0_c, hw1_c,
+                                                              hw0_f, pair_offset=pair_offset, chunks=chunks))
 
 
 def unpack_records(buf, capacity, world):

@@ -500,6 +500,18 @@ def test_match_head_pipeline_records(window_dtype):
     rec2, _, _ = head.match_host(fc0.pin_memory(), fc1.pin_memory(), ff0.pin_memory(), ff1.pin_memory(),
                                  hw_i, hw_c, hw_c, hw_f, pair_offset=100)
     assert np.array_equal(rec2.view(np.uint8), rec.view(np.uint8))
+    # pipelined form: two calls outstanding, collected in order; a third submit before a collect is refused
+    host = [t.pin_memory() for t in (fc0, fc1, ff0, ff1)]
+    t1 = head.match_host_submit(*host, hw_i, hw_c, hw_c, hw_f, pair_offset=100)
+    t2 = head.match_host_submit(*host, hw_i, hw_c, hw_c, hw_f, pair_offset=7)
+    with pytest.raises(_lib.FmError):
+        head.match_host_submit(*host, hw_i, hw_c, hw_c, hw_f)
+    r1 = head.match_host_result(t1)[0].copy()
+    t3 = head.match_host_submit(*host, hw_i, hw_c, hw_c, hw_f, pair_offset=100)
+    r2 = head.match_host_result(t2)[0].copy()
+    r3 = head.match_host_result(t3)[0].copy()
+    assert np.array_equal(r1.view(np.uint8), rec.view(np.uint8)) and np.array_equal(r3.view(np.uint8), rec.view(np.uint8))
+    assert np.array_equal(r2["pair"], rec["pair"] - 93) and np.array_equal(r2["x0"], rec["x0"])
 
 
 def test_gather_large_batch_vs_oracle_windows():
@@ -523,3 +535,36 @@ def test_gather_large_batch_vs_oracle_windows():
         w0, w1 = pre(ff0.to(DEV), ff1.to(DEV), fc0.to(DEV, tok_dtype), fc1.to(DEV, tok_dtype), data)
         compare.check_windows(w0, r0)
         compare.check_windows(w1, r1)
+
+
+def test_overlapped_gather_staging_world1_nccl():
+    """pipeline.OverlappedGather over NCCL with one rank (the box the driver tests on has one GPU): the two staging
+    slots, stage() twice before a launch(), reuse of a slot two exchanges later, gather-to-root and all_gather."""
+    import torch.distributed as dist
+    from featurematching_b200 import pipeline
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29541")
+    dev = torch.device(DEV)
+    dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
+    try:
+        cap = 1000
+        n = (cap + 1) * _lib.RECORD_BYTES
+        g = torch.Generator(device="cpu").manual_seed(1)
+        bufs = [torch.randint(0, 255, (n + 64,), dtype=torch.uint8, generator=g).to(dev) for _ in range(5)]
+        for dst in (0, None):
+            og = pipeline.OverlappedGather(dev, dst=dst)
+            outs = []
+            for k, b in enumerate(bufs):
+                og.stage(b, cap)
+                b2 = b.clone()
+                b.zero_()                      # the caller's buffer is free right after stage()
+                if k != 1:                     # k = 1: staged twice without a launch -> the older one is sent first
+                    outs.append((og.launch(), b2))
+                bufs[k] = b2
+            out = og.finish()
+            torch.cuda.synchronize()
+            assert out.numel() == n and torch.equal(out, bufs[-1][:n])
+            for o, ref in outs[:-1]:
+                assert o is None or o.numel() == n
+    finally:
+        dist.destroy_process_group()
