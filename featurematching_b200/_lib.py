@@ -48,6 +48,7 @@ SIGNATURES = {
     "fm_fine_transformer": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _Z, _P]),
     "fm_coarse_transformer_workspace_bytes": (_Z, [_I, _I, _I, _I]),
     "fm_coarse_transformer": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _Z, _P]),
+    "fm_backbone_emit": (_I, [_P, _c.c_longlong, _I, _I, _P, _P, _F, _P, _P, _P, _P]),
     "fm_pose_workspace_bytes": (_Z, [_I, _I, _I]),
     "fm_pose_from_matches": (_I, [_P, _P, _P, _I, _P, _I, _I, _P, _F, _I, _I, _c.c_uint32, _P, _P, _P, _P, _P, _P, _P,
                                   _Z, _P]),

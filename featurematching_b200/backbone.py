@@ -217,25 +217,54 @@ class SwinUNetBackbone(nn.Module):
         self.liner_middle = nn.Linear(128, 256, bias=False)
         self.liner_end = nn.Linear(64, 64, bias=False)
 
-    def forward_maps(self, img):
-        """img [B, in_chans, H, W] -> (coarse [B, H/8, W/8, 256], fine [B, H/2, W/2, 64]) channels-last."""
+    @staticmethod
+    def _emit_head(y, norm, linear, bf16):
+        """LayerNorm + Linear of one output head through fm_backbone_emit (csrc/backbone_emit.cu): y [B, H, W, Cin]
+        fp32 channels-last -> [B, H, W, Cout] channels-last, fp32 (coarse tokens) or bf16 (fine map), one pass."""
+        from . import _lib
+        lib = _lib.load()
+        y = y.float().contiguous()
+        B, H, W, Cin = y.shape
+        Cout = linear.weight.shape[0]
+        out = torch.empty(B, H, W, Cout, dtype=torch.bfloat16 if bf16 else torch.float32, device=y.device)
+        p = [t.detach().float().contiguous() for t in (norm.weight, norm.bias, linear.weight)]
+        with torch.cuda.device(y.device):
+            rc = lib.fm_backbone_emit(_lib.ptr(y), B * H * W, Cin, Cout, _lib.ptr(p[0]), _lib.ptr(p[1]), float(norm.eps),
+                                      _lib.ptr(p[2]), None if bf16 else _lib.ptr(out), _lib.ptr(out) if bf16 else None,
+                                      _lib.stream_ptr(y.device))
+        _lib.check(rc, "fm_backbone_emit")
+        return out
+
+    def forward_maps(self, img, fused_heads=False):
+        """img [B, in_chans, H, W] -> (coarse [B, H/8, W/8, 256], fine [B, H/2, W/2, 64]) channels-last.
+        fused_heads (CUDA only): the two output heads (swin...py:689-702) run as fm_backbone_emit -- the fine map
+        comes out as bf16, the layout and type the window gather reads; the coarse tokens as fp32."""
         x = self.patch_embed(img)
         for layer, norm in zip(self.layers, self.norm_down):
             x = norm(layer(x))
         coarse = fine = None
         for j, (layer, norm) in enumerate(zip(self.layers_up, self.norm_up)):
-            x = norm(layer(x))
-            if j == 0:
-                coarse = self.liner_middle(x)
-            elif j == 2:
-                fine = self.liner_end(x)
+            y = layer(x)
+            if fused_heads and j == 0:
+                coarse = self._emit_head(y, norm, self.liner_middle, bf16=False)
+            elif fused_heads and j == 2:
+                fine = self._emit_head(y, norm, self.liner_end, bf16=True)
+                break                          # nothing else reads the last LayerNorm
+            x = norm(y)
+            if not fused_heads:
+                if j == 0:
+                    coarse = self.liner_middle(x)
+                elif j == 2:
+                    fine = self.liner_end(x)
         return coarse, fine
 
     def forward(self, img, emit_bf16=False):
         """Returns [out_c, out_f] with the reference's logical shapes [B, 256, H/8, W/8] and
         [B, 64, H/2, W/2] (swin…py:704), stored channels-last.  emit_bf16: out_f in bf16 -- exactly
-        what the window gather reads, so FinePreprocess.to_channels_last_bf16 becomes a no-op."""
-        coarse, fine = self.forward_maps(img)
-        if emit_bf16:
+        what the window gather reads, so FinePreprocess.to_channels_last_bf16 becomes a no-op; on CUDA the two
+        heads then run as the fused emission kernel."""
+        fused = bool(emit_bf16) and img.is_cuda
+        coarse, fine = self.forward_maps(img, fused_heads=fused)
+        if emit_bf16 and not fused:
             fine = fine.to(torch.bfloat16)
         return [coarse.permute(0, 3, 1, 2), fine.permute(0, 3, 1, 2)]

@@ -617,6 +617,23 @@ int fm_pose_from_matches(const int64_t* b_ids, const float* mkpts0_f, const floa
     return FM_OK;
 }
 
+int fm_backbone_emit(const float* x, long long rows, int Cin, int Cout, const float* ln_weight, const float* ln_bias,
+                     float ln_eps, const float* linear_weight, float* out_f32, void* out_bf16, void* stream) {
+    if (!x || !ln_weight || !ln_bias || !linear_weight || (!out_f32 && !out_bf16)) { set_error("null pointer argument"); return FM_ERR_BAD_ARG; }
+    if (rows < 0 || !(ln_eps > 0.f)) { set_error("bad argument to fm_backbone_emit (rows >= 0, ln_eps > 0)"); return FM_ERR_BAD_ARG; }
+    if (!backbone_emit_supported(Cin, Cout)) {
+        set_error("fm_backbone_emit supports the two heads of the backbone: 64 -> 64 and 128 -> 256 (got %d -> %d)", Cin, Cout);
+        return FM_ERR_UNSUPPORTED;
+    }
+    if (rows == 0) return FM_OK;
+    const int sms = sm_count();
+    if (sms <= 0) { set_error("no CUDA device available (this library has no CPU path)"); return FM_ERR_CUDA; }
+    cudaError_t e = launch_backbone_emit(x, rows, Cin, Cout, ln_weight, ln_bias, ln_eps, linear_weight, out_f32, out_bf16,
+                                         sms, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "backbone_emit launch");
+    return FM_OK;
+}
+
 int fm_profile_enable(int on) {
     std::lock_guard<std::mutex> lk(g_timers.mu);
     g_timers.on = on != 0;

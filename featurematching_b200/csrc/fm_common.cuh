@@ -129,6 +129,11 @@ cudaError_t launch_coarse_finish_lse(const CoarseResolveParams& p, const CoarseW
 cudaError_t launch_coarse_resolve(const CoarseResolveParams& p, const CoarseWorkspace& w,
                                   cudaStream_t st);
 
+bool backbone_emit_supported(int Cin, int Cout);
+cudaError_t launch_backbone_emit(const float* x, long long rows, int Cin, int Cout, const float* ln_w, const float* ln_b,
+                                 float eps, const float* lin_w, float* out_f32, void* out_bf16, int num_sms,
+                                 cudaStream_t st);
+
 void set_error(const char* fmt, ...);
 
 // Kernel launches issued by this library since load (fm_launch_count): every launcher bumps it right after a

@@ -231,6 +231,19 @@ FM_API int fm_pack_matches_append(const int64_t* b_ids, const int64_t* i_ids, co
                                   int32_t* chunk_counts, int chunk_index, int total_capacity,
                                   void* records, void* stream);
 
+/* ---------------------------------------------------------------- backbone output heads
+ * The hand-over from the Swin-UNet to the matcher, network/backbone/swin_backbone_modify_unetarchecture.py:689-702:
+ *   x = norm_up[j](x); out = liner_middle(x) (128 -> 256, coarse tokens) | liner_end(x) (64 -> 64, fine map);
+ *   out.view(-1, Wh, Ww, C).permute(0, 3, 1, 2).contiguous()
+ * as one pass per head: LayerNorm(Cin, eps) + Linear(Cin -> Cout, no bias) on `rows` = B * Wh * Ww rows of
+ * x [rows, Cin] fp32, written row-major [rows, Cout] -- i.e. CHANNELS-LAST maps / token sequences, the layouts the
+ * matcher's kernels read -- as fp32 (out_f32, the coarse transformer's input) and / or bf16 (out_bf16, the window
+ * gather's input); either may be NULL.  linear_weight [Cout, Cin] row-major (nn.Linear.weight).
+ * Supported (Cin, Cout): (64, 64), (128, 256). */
+FM_API int fm_backbone_emit(const float* x, long long rows, int Cin, int Cout, const float* ln_weight,
+                            const float* ln_bias, float ln_eps, const float* linear_weight, float* out_f32,
+                            void* out_bf16, void* stream);
+
 /* ---------------------------------------------------------------- pose from matches
  * Relative pose of every frame pair of a batch from its fine matches, on the device -- the consumer of
  * mkpts*_f that the reference runs through OpenCV on the host after a device->host copy:

@@ -218,3 +218,40 @@ def test_matcher_low_thr_strict_vs_oracle_on_own_features(golden):
     r0, r1 = mo.fine_match(w0, w1, data["mkpts0_c"].cpu(), data["mkpts1_c"].cpu(), fin, hw_i, hw_f)
     compare.check_fine(data["mkpts0_f"], data["mkpts1_f"], r0, r1)
     assert ties <= 4
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("head", [(64, 64, True), (128, 256, False)], ids=["fine_64x64_bf16", "coarse_128x256_f32"])
+@pytest.mark.parametrize("rows", [1, 37, 4099])
+def test_backbone_emit_kernel_vs_torch(head, rows):
+    """fm_backbone_emit (LayerNorm + Linear of the backbone's two output heads, swin...py:689-702) against the
+    same two torch modules in fp32: 2e-5 relative on the fp32 head; the bf16 head within one bf16 rounding step of
+    torch's fp32 result (the kernel rounds its own fp32 sum once)."""
+    import torch.nn as nn
+    from featurematching_b200.backbone import SwinUNetBackbone
+    Cin, Cout, bf16 = head
+    torch.manual_seed(rows + Cin)
+    norm, lin = nn.LayerNorm(Cin), nn.Linear(Cin, Cout, bias=False)
+    with torch.no_grad():
+        norm.weight.uniform_(0.5, 1.5); norm.bias.uniform_(-0.3, 0.3)
+    y = torch.randn(1, 1, rows, Cin) * 2.0 + 0.5
+    ref = lin(norm(y)).detach()
+    out = SwinUNetBackbone._emit_head(y.cuda(), norm.cuda(), lin.cuda(), bf16=bf16).cpu()
+    assert out.shape == ref.shape and out.dtype == (torch.bfloat16 if bf16 else torch.float32)
+    tol = 2e-5 * ref.abs().max() + (ref.abs() * 2.0 ** -8 if bf16 else 0.0)
+    assert ((out.float() - ref).abs() <= tol).all(), f"max err {(out.float() - ref).abs().max():.3e}"
+
+
+@pytest.mark.gpu
+def test_backbone_fused_heads_equal_eager_heads():
+    """The whole backbone restatement with the emission kernel vs the same module in eager PyTorch on the GPU."""
+    from featurematching_b200.backbone import SwinUNetBackbone
+    torch.manual_seed(2)
+    bb = SwinUNetBackbone().eval().cuda()
+    img = torch.rand(2, 3, 128, 160, device="cuda")
+    with torch.no_grad():
+        c0, f0 = bb.forward_maps(img, fused_heads=False)
+        c1, f1 = bb.forward_maps(img, fused_heads=True)
+    assert c1.dtype == torch.float32 and f1.dtype == torch.bfloat16 and c1.shape == c0.shape and f1.shape == f0.shape
+    assert (c1 - c0).abs().max() <= 2e-5 * c0.abs().max()
+    assert ((f1.float() - f0).abs() <= 2e-5 * f0.abs().max() + f0.abs() * 2.0 ** -8).all()
