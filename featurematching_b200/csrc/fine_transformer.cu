@@ -24,6 +24,7 @@
 //   [192,256) X operand (hi 32 + lo 32); overwritten by the hi half of the hidden activations
 //             and rewritten with the updated x at the end of every pass
 #include <algorithm>
+#include <atomic>
 
 #include "fm_common.cuh"
 #include "fm_ptx.cuh"
@@ -105,7 +106,16 @@ __device__ __forceinline__ void store_operand32(uint32_t thi, uint32_t tlo, cons
     tmem_st_32x16(tlo, lo);
 }
 // LayerNorm over 64 channels from the two halves' statistics (Chan's combination), eps 1e-5
-__device__ __forceinline__ void layer_norm32(float (&v)[32], float2 mine, float2 other, const float* w, const float* b) {
+// The LayerNorm parameters of the layer being run sit in the CONSTANT bank (copied there from the packed blob,
+// stream-ordered, before the launch): read from shared memory they cost every warp 128 crossbar cycles per pass on a
+// kernel whose shared-memory data pipe is 61 % busy (r02 ncu) -- 4.8 % of the kernel's time (A/B with the loads
+// compiled out).  kLnSlots rotating slots: a launch on another stream must be kLnSlots launches behind before it
+// could overwrite the parameters of a kernel still running.
+constexpr int kLnSlots = 16;
+__constant__ float c_tf_ln[kLnSlots][256];   // norm1.weight, norm1.bias, norm2.weight, norm2.bias (4 x 64)
+
+// w, b: offsets of this thread's 32 weights / biases in c_tf_ln[slot]
+__device__ __forceinline__ void layer_norm32(float (&v)[32], float2 mine, float2 other, int slot, int w, int b) {
     const float mean = 0.5f * (mine.x + other.x);
     const float dm = mine.x - other.x;
     const float var = (mine.y + other.y + dm * dm * 16.f) * (1.f / 64.f);
@@ -113,8 +123,8 @@ __device__ __forceinline__ void layer_norm32(float (&v)[32], float2 mine, float2
     const uint64_t r2 = pack2(rstd, rstd), nm = pack2(-mean, -mean);
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {   // y = v * (rstd w) + (b - mean rstd w), two channels per instruction
-        const float4 ww = *reinterpret_cast<const float4*>(w + i);
-        const float4 bb = *reinterpret_cast<const float4*>(b + i);
+        const float4 ww = make_float4(c_tf_ln[slot][w + i], c_tf_ln[slot][w + i + 1], c_tf_ln[slot][w + i + 2], c_tf_ln[slot][w + i + 3]);
+        const float4 bb = make_float4(c_tf_ln[slot][b + i], c_tf_ln[slot][b + i + 1], c_tf_ln[slot][b + i + 2], c_tf_ln[slot][b + i + 3]);
         const uint64_t a0 = mul2(pack2(ww.x, ww.y), r2), a1 = mul2(pack2(ww.z, ww.w), r2);
         unpack2(fma2(pack2(v[i], v[i + 1]), a0, fma2(a0, nm, pack2(bb.x, bb.y))), v[i], v[i + 1]);
         unpack2(fma2(pack2(v[i + 2], v[i + 3]), a1, fma2(a1, nm, pack2(bb.z, bb.w))), v[i + 2], v[i + 3]);
@@ -165,6 +175,7 @@ struct TfParams {
     int capacity;
     int WW;
     const uint8_t* blob;
+    int ln_slot;            // c_tf_ln slot holding this layer's LayerNorm parameters
 };
 
 // ---------------------------------------------------------------- one encoder layer
@@ -303,7 +314,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
         const int row = q * 32 + lane;                             // TMEM lane
         const uint32_t tl = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + slot * kSlotCols;
         const uint32_t bar_id = 1 + slot;
-        const float* ln = reinterpret_cast<const float*>(blob + kOffLn) + 32 * g;
+        const int ln_slot = p.ln_slot, ln_off = 32 * g;
         float2* lnrow = lnx + (slot * 128 + row) * 2;
         float* kvm = kvm_all + slot * 2 * 64 * 8;                  // this slot's KV matrices / key sums
         float* ksum = ksum_all + slot * 2 * 64;
@@ -331,7 +342,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
             if (r < WW && m < M)
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(p.in[side] + (static_cast<size_t>(m) * WW + r) * kC + 32 * g));
         };
-        mbar_wait(&ctl->w_full, 0);   // LayerNorm parameters live in the blob
+        // (the LayerNorm parameters come from the constant bank: the epilogue warps do not wait for the weight blob)
 
         [[maybe_unused]] int tn = 0;
         [[maybe_unused]] const bool tr = (warp & 7) == 0 && lane == 0;
@@ -496,7 +507,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                 float2 mine = local_stats(y);
                 lnrow[g] = mine;
                 named_bar_sync(bar_id, kSlotThreads);
-                layer_norm32(y, mine, lnrow[g ^ 1], ln, ln + 64);
+                layer_norm32(y, mine, lnrow[g ^ 1], ln_slot, ln_off, ln_off + 64);
                 store_operand32(tl + 128 + 16 * g, tl + 160 + 16 * g, y);
                 signal_mma();
                 TFE(10);
@@ -524,7 +535,7 @@ __global__ void __launch_bounds__(kTfThreads, 1) tf_layer_kernel(const TfParams 
                 mine = local_stats(y);
                 lnrow[g] = mine;
                 named_bar_sync(bar_id, kSlotThreads);
-                layer_norm32(y, mine, lnrow[g ^ 1], ln + 128, ln + 192);
+                layer_norm32(y, mine, lnrow[g ^ 1], ln_slot, ln_off + 128, ln_off + 192);
 #pragma unroll
                 for (int i = 0; i < 32; ++i) x[i] += y[i];
                 TFE(14);
@@ -586,6 +597,11 @@ cudaError_t launch_fine_transformer(const float* win0, const float* win1, const 
         p.out[0] = out0; p.out[1] = out1;
         p.count = count; p.capacity = capacity; p.WW = WW;
         p.blob = blobs + static_cast<size_t>(l) * kBlobBytes;
+        static std::atomic<unsigned> next_slot{0};
+        p.ln_slot = static_cast<int>(next_slot.fetch_add(1, std::memory_order_relaxed) % kLnSlots);
+        e = cudaMemcpyToSymbolAsync(c_tf_ln, p.blob + kOffLn, 256 * sizeof(float), static_cast<size_t>(p.ln_slot) * 256 * sizeof(float),
+                                    cudaMemcpyDeviceToDevice, st);
+        if (e != cudaSuccess) return e;
         kern[kinds[l] ? 1 : 0]<<<grid, kTfThreads, kTfSmem, st>>>(p); count_launch();
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
