@@ -455,6 +455,11 @@ cudaError_t launch_coarse_resolve(const CoarseResolveParams& p, const CoarseWork
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, coarse_resolve_kernel, kResolveThreads, 0);
     if (e != cudaSuccess) return e;
     if (d.num_pools > kMaxPools) { set_error("too many candidate pools for the resolve kernel"); return cudaErrorInvalidValue; }
+    // the kernel indexes records, rows and columns with 32-bit integers
+    if (1LL * d.num_pools * d.hot_cap >= (1LL << 31) || 1LL * d.B * d.N0 >= (1LL << 31) || 1LL * d.B * d.N1 >= (1LL << 31)) {
+        set_error("coarse problem too large for the resolve kernel's 32-bit indices (B * N, pools * hot_cap must be < 2^31)");
+        return cudaErrorInvalidValue;
+    }
     const int resident = std::max(1, sms * per_sm);
     const int grid = std::min(resident, kMaxResolveBlocks);
     ResolveWs rw{w.hot_meta, w.hot_dots, w.hot_count, w.l2row, w.l2col, w.rowbest, w.colbest,
