@@ -399,7 +399,9 @@ int fm_fine_to_nhwc_bf16(const void* src, int src_dtype, int B, int C, int H, in
 
 size_t fm_fine_gather_workspace_bytes(int B, int N0, int N1, int Cc, int Cf, int featc_dtype) {
     if (B < 1 || N0 < 1 || N1 < 1 || Cc < 1 || !dtype_ok(featc_dtype)) return 0;
-    if (!fine_gather_tc_supported(Cf, Cc, 7)) return 0;   // the SIMT path needs no workspace
+    // The size does not depend on the window: every window the tensor-core path takes (2 <= W <= 7) needs the same
+    // carve, and for a window it does not take (W = 8) the workspace is merely unused (the SIMT path needs none).
+    if (!fine_gather_tc_supported(Cf, Cc, 7)) return 0;
     return fine_gather_tc_workspace_bytes(B, N0, N1, Cc, featc_dtype == FM_DTYPE_F32);
 }
 

@@ -188,3 +188,17 @@ def test_install_swaps_the_five_modules_and_keeps_the_state_dict():
             assert torch.equal(after[k], v), k
     assert set(net._fm_reference) == {"coarse", "coarse_matching", "fine_preprocess", "fine", "fine_matching"}
     assert not net.training
+
+
+def test_backbone_emit_argument_errors(lib):
+    buf = (ctypes.c_char * 4096)()
+    p = ctypes.c_void_p((ctypes.addressof(buf) + 255) & ~255)
+    call = lambda rows=10, Cin=64, Cout=64, eps=1e-5, x=p, o32=p, o16=None: lib.fm_backbone_emit(
+        x, rows, Cin, Cout, p, p, eps, p, o32, o16, None)
+    assert call(x=None) == -1 and call(o32=None, o16=None) == -1            # FM_ERR_BAD_ARG
+    assert call(rows=-1) == -1 and call(eps=0.0) == -1
+    assert call(Cin=96) == -4 and b"64 -> 64" in lib.fm_last_error_string()   # FM_ERR_UNSUPPORTED
+    assert call(Cin=128, Cout=64) == -4
+    assert call(rows=0) == 0                                                  # nothing to do
+    if not torch.cuda.is_available():
+        assert call() == -3 and call(Cin=128, Cout=256) == -3                 # FM_ERR_CUDA: no CPU path
