@@ -57,9 +57,9 @@ __global__ void __launch_bounds__(256) finish_lse_kernel(CoarseDims d, float a2,
     const float maxn0 = maxnorm[b * 2 + 0], maxn1 = maxnorm[b * 2 + 1];
     int lost = 0;
     if (t < d.N0) {
-        const float* rp = rowpart + static_cast<size_t>(b) * d.NB * 2 * d.N0pad + t;
+        const float* rp = rowpart + static_cast<size_t>(b) * d.NB * kColGroups * d.N0pad + t;
         float s = 0.f;
-        for (int k = 0; k < d.NB * 2; ++k) s += rp[static_cast<size_t>(k) * d.N0pad];
+        for (int k = 0; k < d.NB * kColGroups; ++k) s += rp[static_cast<size_t>(k) * d.N0pad];
         const float ci = score_bound2(norm0[static_cast<size_t>(b) * d.N0pad + t], maxn1, a2) - kHead2;
         // a sum below 2^-100 has lost relative precision to flush-to-zero: the token is "lost"
         const bool ok = s >= 7.8886e-31f && s < INFINITY;

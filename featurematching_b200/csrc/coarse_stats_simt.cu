@@ -55,8 +55,8 @@ __global__ void __launch_bounds__(256) coarse_stats_simt_kernel(const __nv_bfloa
         float rowsum = 0.f;
         float full = 0.f;
         if (kPhase == 1) {
-            const float* rp = p.rowpart + static_cast<size_t>(b) * d.NB * 2 * d.N0pad + i;
-            for (int k = 0; k < d.NB * 2; ++k) full += rp[static_cast<size_t>(k) * d.N0pad];
+            const float* rp = p.rowpart + static_cast<size_t>(b) * d.NB * kColGroups * d.N0pad + i;
+            for (int k = 0; k < d.NB * kColGroups; ++k) full += rp[static_cast<size_t>(k) * d.N0pad];
         }
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -82,8 +82,8 @@ __global__ void __launch_bounds__(256) coarse_stats_simt_kernel(const __nv_bfloa
             }
         }
         if (kPhase == 0) {
-            const int slot = (j0 + tx * 4) / 128;   // = 2 * nblk + column half, as K1 lays it out
-            atomicAdd(p.rowpart + (static_cast<size_t>(b) * d.NB * 2 + slot) * d.N0pad + i, rowsum);
+            const int slot = (j0 + tx * 4) / kGroupCols;   // = kColGroups * nblk + column group, as K1 lays it out
+            atomicAdd(p.rowpart + (static_cast<size_t>(b) * d.NB * kColGroups + slot) * d.N0pad + i, rowsum);
             // column sums of this row go to the split its tile belongs to
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
@@ -108,7 +108,7 @@ cudaError_t launch_coarse_stats_simt(const __nv_bfloat16* f0, const __nv_bfloat1
             e = cudaFuncSetAttribute(coarse_stats_simt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024);
         if (e != cudaSuccess) return e;
     }
-    cudaError_t e = cudaMemsetAsync(p.rowpart, 0, sizeof(float) * d.B * d.NB * 2 * d.N0pad, st);
+    cudaError_t e = cudaMemsetAsync(p.rowpart, 0, sizeof(float) * d.B * d.NB * kColGroups * d.N0pad, st);
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(p.colpart, 0, sizeof(float) * d.B * d.S * d.N1pad, st);
     if (e != cudaSuccess) return e;

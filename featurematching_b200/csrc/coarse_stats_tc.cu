@@ -39,9 +39,22 @@ namespace fm {
 namespace {
 
 constexpr int kKC = kMaxC / kChunkK;   // channel chunks of the resident operand (4)
+constexpr int kChunks = kGroupCols / 32;   // 32-column chunks of a thread's accumulator row
+// registers per epilogue thread after the control warpgroup gave its share back (setmaxnreg): wide 8 warps x 232,
+// narrow 12 warps x 152 (64 column accumulators + two 32-word TMEM load buffers + the rest)
+constexpr int kEpiRegs = kColGroups == 2 ? 232 : 152;
+
+// -DK1_TRACE: clock64 stamps of CTA 0 (epilogue warp 0 of column group 0, the MMA thread, the TMA thread) per tile
+#ifdef K1_TRACE
+constexpr int kTrTiles = 96, kTrPts = 8;
+__device__ long long g_k1_trace[3][kTrTiles][kTrPts];
+#define K1T(role, n, id) do { if (blockIdx.x == 0 && (n) < kTrTiles) g_k1_trace[role][n][id] = clock64(); } while (0)
+#else
+#define K1T(role, n, id) do {} while (0)
+#endif
 
 struct __align__(16) SmemCtl {
-    float colscratch[kEpiWarps][128];   // first: float4 stores need 16-byte alignment
+    float colscratch[kEpiWarps][kGroupCols];   // first: vector stores need 16-byte alignment
     uint64_t a_full[kAStages];
     uint64_t a_empty[kAStages];
     uint64_t b_full[kKC];
@@ -57,6 +70,33 @@ constexpr size_t kSmemOperands = static_cast<size_t>(kBChunkBytes) * kKC +
 constexpr size_t kSmemBytes = kSmemOperands + sizeof(SmemCtl) + 1024;  // + alignment slack
 static_assert(kSmemBytes <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
 
+// 2^x for two scores on the FMA pipe (an OPTION, off by default): x = n + f, n = round(x), f in [-0.5, 0.5]; 2^f by a
+// degree-4 minimax polynomial (max relative error 2.7e-6), 2^n by an integer add into the exponent field; scores
+// clamped at -126.  K1_POLY_MASK: bit k = pair k of a 32-column chunk goes through here instead of MUFU.EX2.
+// Measured (r02, 32 pairs 640x512): 0 / 12.5 / 25 / 50 % of the scores -> 0.412 / 0.404 / 0.414 / 0.443 ms: inside the
+// chunk phase the XU pipe is 80 % busy, but the epilogue as a whole is not MUFU-bound -- 2 % at best,
+// not worth a second exponential in the numerics.
+#ifndef K1_POLY_MASK
+#define K1_POLY_MASK 0x0000u
+#endif
+__device__ __forceinline__ void ex2_poly2(uint64_t x2, float& pl, float& ph) {
+    float xl, xh;
+    unpack2(x2, xl, xh);
+    const uint64_t xc = pack2(fmaxf(xl, -126.f), fmaxf(xh, -126.f));
+    const uint64_t magic = pack2(12582912.f, 12582912.f);          // 1.5 * 2^23: the sum's low mantissa bits = round(x)
+    const uint64_t t = add2(xc, magic);
+    const uint64_t f = sub2(xc, sub2(t, magic));
+    uint64_t q = fma2(pack2(0.009570082649588585f, 0.009570082649588585f), f, pack2(0.05591784417629242f, 0.05591784417629242f));
+    q = fma2(q, f, pack2(0.240247443318367f, 0.240247443318367f));
+    q = fma2(q, f, pack2(0.6931217908859253f, 0.6931217908859253f));
+    q = fma2(q, f, pack2(0.9999992847442627f, 0.9999992847442627f));
+    float ql, qh, tl, th;
+    unpack2(q, ql, qh);
+    unpack2(t, tl, th);
+    pl = __uint_as_float(__float_as_uint(ql) + (__float_as_uint(tl) << 23));
+    ph = __uint_as_float(__float_as_uint(qh) + (__float_as_uint(th) << 23));
+}
+
 // One 32-column chunk of the thread's accumulator row.  Returns the chunk's largest p (first pass) or, in the
 // exact pass (kExact; `lc` = log2 column soft-max sums of the chunk's 32 columns), its largest
 // 2 log2(p) - l2col_j = log2(conf_ij) + (l2row_i - 2 c_i): the confidence itself up to a per-row constant.
@@ -68,9 +108,13 @@ __device__ __forceinline__ float process_chunk(const uint32_t (&r)[32], uint64_t
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
         uint64_t t2 = fma2(pack2(__uint_as_float(r[2 * k]), __uint_as_float(r[2 * k + 1])), a2p, biasp);
-        float tl, th;
+        float tl, th, pl, ph;
         unpack2(t2, tl, th);
-        const float pl = ex2_approx(tl), ph = ex2_approx(th);
+        if ((K1_POLY_MASK >> k) & 1u) {
+            ex2_poly2(t2, pl, ph);
+        } else {
+            pl = ex2_approx(tl); ph = ex2_approx(th);
+        }
         const uint64_t p2 = pack2(pl, ph);
         if (k & 1) racc1 = add2(racc1, p2); else racc0 = add2(racc0, p2);
         colacc[k] = fma2(p2, wp, colacc[k]);
@@ -176,8 +220,10 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                 const int mt1 = min(mt0 + d.tiles_per_split, d.MT);
                 for (int mt = mt0; mt < mt1; ++mt, ++tile_it) {
                     const uint32_t buf = tile_it & 1, tph = (tile_it >> 1) & 1;
+                    K1T(1, tile_it, 0);
                     mbar_wait(&ctl->t_empty[buf], tph ^ 1);
                     tc_fence_after();
+                    K1T(1, tile_it, 1);
                     const uint32_t d_tmem = tmem_base + buf * kBlockN;
                     for (int kc = 0; kc < KC; ++kc, ++a_it) {
                         const uint32_t s = a_it % kAStages, ph = (a_it / kAStages) & 1;
@@ -196,17 +242,18 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                         if (mt == mt1 - 1) umma_commit(&ctl->b_empty[kc]);   // chunk may be overwritten
                     }
                     umma_commit(&ctl->t_full[buf]);      // accumulator complete
+                    K1T(1, tile_it, 2);
                 }
             }
         }
     }
     } else {
-        reg_alloc<232>();
-        // ===================================================== epilogue: 8 warps, 2 warpgroups
-        const int ew = warp - kCtlWarps;      // 0..7
-        const int wg = ew >> 2;               // column half
+        reg_alloc<kEpiRegs>();
+        // ===================================================== epilogue: one warpgroup per column group
+        const int ew = warp - kCtlWarps;      // 0 .. kEpiWarps - 1
+        const int wg = ew >> 2;               // column group
         const int q = warp & 3;               // TMEM lane quarter this warp may access
-        const int et = threadIdx.x - kCtlWarps * 32;   // 0..255
+        const int et = threadIdx.x - kCtlWarps * 32;   // 0 .. kEpiWarps * 32 - 1
         const uint64_t a2p = pack2(p.a2, p.a2);
         uint2* const pool_meta = p.hot_meta + static_cast<size_t>(blockIdx.x) * d.hot_cap;
         float* const pool_dots = p.hot_dots + static_cast<size_t>(blockIdx.x) * d.hot_cap * kHotChunk;
@@ -217,19 +264,19 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
             const int mt1 = min(mt0 + d.tiles_per_split, d.MT);
             const float maxn0 = p.maxnorm[b * 2 + 0], maxn1 = p.maxnorm[b * 2 + 1];
             const float cref = score_bound2(maxn0, maxn1, p.a2) - kHead2;
-            // valid columns of this warpgroup's half of the block
-            const int col0 = nblk * kBlockN + wg * 128;
-            const int nvalid = max(0, min(128, d.N1 - col0));
-            float* rowpart = p.rowpart + (static_cast<size_t>(b) * d.NB * 2 + nblk * 2 + wg) * d.N0pad;
+            // valid columns of this warpgroup's column group
+            const int col0 = nblk * kBlockN + wg * kGroupCols;
+            const int nvalid = max(0, min(kGroupCols, d.N1 - col0));
+            float* rowpart = p.rowpart + (static_cast<size_t>(b) * d.NB * kColGroups + nblk * kColGroups + wg) * d.N0pad;
 
-            uint64_t colacc[64];
+            uint64_t colacc[kGroupCols / 2];
 #pragma unroll
-            for (int k = 0; k < 64; ++k) colacc[k] = 0ull;
+            for (int k = 0; k < kGroupCols / 2; ++k) colacc[k] = 0ull;
 
             // token norm of this thread's row, fetched one tile ahead (N0pad rows exist)
             const float* norm_b = p.norm0 + static_cast<size_t>(b) * d.N0pad + q * 32 + lane;
             float n0_next = __ldg(norm_b + mt0 * kTileM);
-            // exact pass: log2 soft-max sums of this pair's rows and of this warpgroup's 128 columns (the l2col
+            // exact pass: log2 soft-max sums of this pair's rows and of this warpgroup's columns (the l2col
             // buffer has kBlockN floats of slack, columns >= N1 carry p = 0 and can never be hot)
             const float* l2row_b = kExact ? p.l2row + static_cast<size_t>(b) * d.N0 : nullptr;
             const float* lcol = kExact ? p.l2col + static_cast<size_t>(b) * d.N1 + col0 : nullptr;
@@ -245,34 +292,28 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                 const float wi = rvalid ? ex2_approx(ci - cref) : 0.f;  // <= 1
                 const uint64_t biasp = pack2(bias, bias), wp = pack2(wi, wi);
 
+                const bool k1tr = ew == 0 && lane == 0;
+                if (k1tr) K1T(0, tile_it, 0);
                 mbar_wait(&ctl->t_full[buf], tph);
                 tc_fence_after();
-                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * kBlockN + wg * 128;
+                if (k1tr) K1T(0, tile_it, 1);
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * kBlockN + wg * kGroupCols;
 
                 uint64_t racc0 = 0ull, racc1 = 0ull;
-                float cm[4];
+                float cm[kChunks];
                 uint32_t ra[32], rb[32];
                 tmem_ld_32x32(taddr, ra);
-                // chunk 0
-                tmem_ld_wait_dep(ra);
-                tmem_ld_32x32(taddr + 32, rb);
-                if (nvalid < 32) mask_chunk(ra, nvalid);
-                cm[0] = process_chunk<kExact>(ra, a2p, biasp, wp, colacc, racc0, racc1, lcol + 0);
-                // chunk 1
-                tmem_ld_wait_dep(rb);
-                tmem_ld_32x32(taddr + 64, ra);
-                if (nvalid < 64) mask_chunk(rb, nvalid - 32);
-                cm[1] = process_chunk<kExact>(rb, a2p, biasp, wp, colacc + 16, racc0, racc1, lcol + 32);
-                // chunk 2
-                tmem_ld_wait_dep(ra);
-                tmem_ld_32x32(taddr + 96, rb);
-                if (nvalid < 96) mask_chunk(ra, nvalid - 64);
-                cm[2] = process_chunk<kExact>(ra, a2p, biasp, wp, colacc + 32, racc0, racc1, lcol + 64);
-                // chunk 3
-                tmem_ld_wait_dep(rb);
-                if (nvalid < 128) mask_chunk(rb, nvalid - 96);
-                cm[3] = process_chunk<kExact>(rb, a2p, biasp, wp, colacc + 48, racc0, racc1, lcol + 96);
+#pragma unroll
+                for (int ch = 0; ch < kChunks; ++ch) {   // chunk ch + 1 is in flight while chunk ch is processed
+                    uint32_t (&cur)[32] = (ch & 1) ? rb : ra;
+                    uint32_t (&nxt)[32] = (ch & 1) ? ra : rb;
+                    tmem_ld_wait_dep(cur);
+                    if (ch + 1 < kChunks) tmem_ld_32x32(taddr + 32 * (ch + 1), nxt);
+                    if (nvalid < 32 * (ch + 1)) mask_chunk(cur, nvalid - 32 * ch);
+                    cm[ch] = process_chunk<kExact>(cur, a2p, biasp, wp, colacc + 16 * ch, racc0, racc1, lcol + 32 * ch);
+                }
 
+                if (k1tr) K1T(0, tile_it, 2);
                 float s0, s1, s2, s3;
                 unpack2(racc0, s0, s1);
                 unpack2(racc1, s2, s3);
@@ -280,14 +321,14 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                 rowpart[mt * kTileM + q * 32 + lane] = rowsum;
 
                 // ---- hot chunks: largest p above the share threshold of the row's partial sum
-                // first pass: the chunk's best p against cand_thr x the row's own 128-column partial sum (weaker
+                // first pass: the chunk's best p against cand_thr x the row's own column-group partial sum (weaker
                 // than the share of the full row sum, hence a superset).  Exact pass: log2 conf_ij =
                 // (2 log2 p - l2col_j) + 2 c_i - l2row_i against log2(cand_thr); a lost row (l2row = INF) is never hot
                 const float share = kExact ? (rvalid ? log2_cand + __ldg(l2row_b + row) - 2.f * ci : INFINITY)
                                            : p.cand_thr * rowsum;
                 uint32_t hot = 0;
 #pragma unroll
-                for (int ch = 0; ch < 4; ++ch) hot |= (cm[ch] > share) ? (1u << ch) : 0u;
+                for (int ch = 0; ch < kChunks; ++ch) hot |= (rvalid && cm[ch] > share) ? (1u << ch) : 0u;
                 uint32_t warp_hot = __reduce_or_sync(0xffffffffu, hot);
                 while (warp_hot) {                                   // warp-uniform, usually 0 or 1 trips
                     const int ch = __ffs(warp_hot) - 1;
@@ -306,30 +347,34 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                         }
                     }
                 }
+                if (k1tr) K1T(0, tile_it, 3);
                 // release the accumulator buffer to the MMA warp
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&ctl->t_empty[buf]);
+                if (k1tr) K1T(0, tile_it, 4);
             }
 
             // ---- unit end: reduce the thread-local column sums over the 32 rows of the warp
-            float v[128];
+            float v[kGroupCols];
 #pragma unroll
-            for (int k = 0; k < 64; ++k) unpack2(colacc[k], v[2 * k], v[2 * k + 1]);
-            reduce_step<64, 16>(v, lane);
-            reduce_step<32, 8>(v, lane);
-            reduce_step<16, 4>(v, lane);
-            reduce_step<8, 2>(v, lane);
-            reduce_step<4, 1>(v, lane);
+            for (int k = 0; k < kGroupCols / 2; ++k) unpack2(colacc[k], v[2 * k], v[2 * k + 1]);
+            reduce_step<kGroupCols / 2, 16>(v, lane);
+            reduce_step<kGroupCols / 4, 8>(v, lane);
+            reduce_step<kGroupCols / 8, 4>(v, lane);
+            reduce_step<kGroupCols / 16, 2>(v, lane);
+            reduce_step<kGroupCols / 32, 1>(v, lane);
             {
-                // lane now holds columns base .. base + 3 summed over the warp's 32 rows
-                const int base = ((lane >> 4) & 1) * 64 + ((lane >> 3) & 1) * 32 + ((lane >> 2) & 1) * 16 +
-                                 ((lane >> 1) & 1) * 8 + (lane & 1) * 4;
-                *reinterpret_cast<float4*>(&ctl->colscratch[ew][base]) = make_float4(v[0], v[1], v[2], v[3]);
+                // lane now holds columns base .. base + kGroupCols / 32 - 1 summed over the warp's 32 rows
+                constexpr int kPer = kGroupCols / 32;
+                const int base = (((lane >> 4) & 1) * 16 + ((lane >> 3) & 1) * 8 + ((lane >> 2) & 1) * 4 +
+                                  ((lane >> 1) & 1) * 2 + (lane & 1)) * kPer;
+#pragma unroll
+                for (int k = 0; k < kPer; ++k) ctl->colscratch[ew][base + k] = v[k];
             }
             named_bar_sync(1, kEpiWarps * 32);
-            {
-                const int g = et >> 7, c = et & 127;
+            if (et < kBlockN) {
+                const int g = et / kGroupCols, c = et % kGroupCols;
                 const float s = (ctl->colscratch[g * 4 + 0][c] + ctl->colscratch[g * 4 + 1][c]) +
                                 (ctl->colscratch[g * 4 + 2][c] + ctl->colscratch[g * 4 + 3][c]);
                 p.colpart[(static_cast<size_t>(b) * d.S + ms) * d.N1pad + nblk * kBlockN + et] = s;
@@ -387,6 +432,12 @@ bool encode_tiled(CUtensorMap* m, CUtensorMapDataType dt, int rank, const void* 
     return fn(m, dt, static_cast<cuuint32_t>(rank), const_cast<void*>(ptr), d, st, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
               swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
+
+#ifdef K1_TRACE
+extern "C" __attribute__((visibility("default"))) int fm_debug_k1_trace(long long* host_out) {
+    return static_cast<int>(cudaMemcpyFromSymbol(host_out, g_k1_trace, sizeof(g_k1_trace)));
+}
+#endif
 
 cudaError_t launch_coarse_stats_tc(const __nv_bfloat16* f0, const __nv_bfloat16* f1,
                                    const CoarseStatsParams& p, int num_sms, cudaStream_t st) {

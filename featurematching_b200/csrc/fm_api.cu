@@ -139,7 +139,7 @@ CoarseWorkspace coarse_workspace(const CoarseDims& d, bool fp32_input, void* bas
     w.zero_bytes = off - w.zero_begin;
     // ---- fully rewritten by every call
     w.norm0 = reinterpret_cast<float*>(take(sizeof(float) * B * d.N0pad));
-    w.rowpart = reinterpret_cast<float*>(take(sizeof(float) * B * d.NB * 2 * d.N0pad));
+    w.rowpart = reinterpret_cast<float*>(take(sizeof(float) * B * d.NB * kColGroups * d.N0pad));
     w.colpart = reinterpret_cast<float*>(take(sizeof(float) * B * d.S * d.N1pad));
     w.l2row = reinterpret_cast<float*>(take(sizeof(float) * B * d.N0));
     w.l2col = reinterpret_cast<float*>(take(sizeof(float) * (B * d.N1 + kBlockN)));   // slack: the exact pass reads whole blocks

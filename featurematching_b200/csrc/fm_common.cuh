@@ -11,15 +11,30 @@ namespace fm {
 
 // ---------------------------------------------------------------- coarse-stage tiling
 constexpr int kTileM = 128;      // image-0 tokens per MMA tile (TMEM lanes)
-constexpr int kBlockN = 256;     // image-1 tokens resident per work unit (TMEM columns)
+// K1's block of image-1 tokens = kColGroups column groups of kGroupCols columns; one epilogue warpgroup (4 warps, one
+// per TMEM lane quarter) per group, a thread owning one accumulator row x kGroupCols columns.  Shipped: 256 = 2 x 128
+// (8 epilogue warps, 232 registers each).  -DFM_K1_NARROW builds 192 = 3 x 64 (12 epilogue warps = 3 per scheduler,
+// 152 registers): measured SLOWER (0.49 vs 0.41 ms, r02) -- the MMA phase of this kernel runs at the rate the
+// shared-memory operand reads allow (SS MMAs: 4 KB of A + 32 N bytes of B per 128 x N x 16 instruction), and a
+// narrower block reads the same A for fewer flops (tools/dbg_k1_trace.py: 3 180 cycles per 128 x 192 tile against
+// 3 250 per 128 x 256 tile on the MMA thread).
+#ifdef FM_K1_NARROW
+constexpr int kColGroups = 3, kGroupCols = 64;
+#else
+constexpr int kColGroups = 2, kGroupCols = 128;
+#endif
+constexpr int kBlockN = kColGroups * kGroupCols;     // image-1 tokens resident per work unit (TMEM columns)
 constexpr int kChunkK = 64;      // bf16 elements per 128-byte swizzle row
 constexpr int kMaxC = 256;       // descriptor channels supported by the resident-B layout
-constexpr int kAStages = 5;      // A-operand ring (16 KB per stage)
+#ifndef FM_K1_ASTAGES
+#define FM_K1_ASTAGES 5
+#endif
+constexpr int kAStages = FM_K1_ASTAGES;      // A-operand ring (16 KB per stage)
 constexpr int kAStageBytes = kTileM * kChunkK * 2;    // 16384
-constexpr int kBChunkBytes = kBlockN * kChunkK * 2;   // 32768
-constexpr int kEpiWarps = 8;
+constexpr int kBChunkBytes = kBlockN * kChunkK * 2;   // 24576 (32768 wide)
+constexpr int kEpiWarps = 4 * kColGroups;
 constexpr int kCtlWarps = 4;     // warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM owner, warp 3 idle
-constexpr int kCoarseThreads = (kCtlWarps + kEpiWarps) * 32;   // 3 warpgroups: control + 2 epilogue
+constexpr int kCoarseThreads = (kCtlWarps + kEpiWarps) * 32;   // control warpgroup + one epilogue warpgroup per column group
 constexpr int kRowSlots = 4;     // in-row slots for exactly tied matches of one image-0 token ...
 constexpr int kTieCap = 16384;   // ... any further ones go to one shared list of (row, j, conf) entries
 
@@ -41,10 +56,10 @@ __device__ __forceinline__ float score_bound2(float n0, float maxn1, float a2) {
 
 struct CoarseDims {
     int B, N0, N1, C, KC;      // KC = C / 64
-    int MT, NB;                // M tiles (128 rows), N blocks (256 columns)
+    int MT, NB;                // M tiles (128 rows), N blocks (kBlockN columns)
     int S, tiles_per_split;    // M range split into S contiguous pieces per (pair, N block)
     int num_units;             // B * NB * S
-    int N0pad, N1pad;          // MT * 128, NB * 256
+    int N0pad, N1pad;          // MT * 128, NB * kBlockN
     int num_pools;             // hot-chunk record pools (= CTAs of the statistics kernel)
     int hot_cap;               // records per pool
 };
@@ -61,7 +76,7 @@ struct CoarseWorkspace {
     __nv_bfloat16* f1b;
     float* norm0;         // [B, N0pad]
     float* maxnorm;       // [B, 2] (float bits, atomicMax)
-    float* rowpart;       // [B, NB * 2, N0pad]
+    float* rowpart;       // [B, NB * kColGroups, N0pad]
     float* colpart;       // [B, S, N1pad]
     uint2* hot_meta;      // [num_pools, hot_cap]  x = b * N0 + i, y = first column / 32
     float* hot_dots;      // [num_pools, hot_cap, 32]  raw <f0_i, f1_j> of the chunk's 32 columns
