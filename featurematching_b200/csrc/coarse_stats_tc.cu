@@ -330,11 +330,7 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
 #pragma unroll
                 for (int ch = 0; ch < kChunks; ++ch) hot |= (rvalid && cm[ch] > share) ? (1u << ch) : 0u;
                 uint32_t warp_hot = __reduce_or_sync(0xffffffffu, hot);
-                while (warp_hot) {                                   // warp-uniform, usually 0 or 1 trips
-                    const int ch = __ffs(warp_hot) - 1;
-                    warp_hot &= warp_hot - 1;
-                    tmem_ld_32x32(taddr + ch * 32, ra);
-                    tmem_ld_wait_dep(ra);
+                auto store_record = [&](int ch, const uint32_t (&raw)[32]) {
                     if ((hot >> ch) & 1) {
                         const int slot = atomicAdd(&ctl->hot_count, 1);
                         if (slot < d.hot_cap) {
@@ -343,15 +339,28 @@ coarse_stats_tc_kernel(const __grid_constant__ CUtensorMap tmap0,
                             uint4* dst = reinterpret_cast<uint4*>(pool_dots + static_cast<size_t>(slot) * kHotChunk);
 #pragma unroll
                             for (int k = 0; k < 8; ++k)
-                                dst[k] = make_uint4(ra[4 * k], ra[4 * k + 1], ra[4 * k + 2], ra[4 * k + 3]);
+                                dst[k] = make_uint4(raw[4 * k], raw[4 * k + 1], raw[4 * k + 2], raw[4 * k + 3]);
                         }
                     }
+                };
+                // The LAST hot chunk (usually the only one) is only re-read from TMEM here; its record (a shared-memory
+                // atomic and 136 bytes of global stores from one or two lanes) is written AFTER the accumulator has
+                // been handed back: every tile has some warp with a hot chunk, and the MMA thread waits for the
+                // slowest of the eight (r02 timeline: the epilogue, not the MMA, sets the tile period).
+                int last_ch = -1;
+                while (warp_hot) {                                   // warp-uniform, usually 0 or 1 trips
+                    const int ch = __ffs(warp_hot) - 1;
+                    warp_hot &= warp_hot - 1;
+                    tmem_ld_32x32(taddr + ch * 32, ra);
+                    tmem_ld_wait_dep(ra);
+                    if (warp_hot) store_record(ch, ra); else last_ch = ch;
                 }
                 if (k1tr) K1T(0, tile_it, 3);
                 // release the accumulator buffer to the MMA warp
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&ctl->t_empty[buf]);
+                if (last_ch >= 0) store_record(last_ch, ra);
                 if (k1tr) K1T(0, tile_it, 4);
             }
 

@@ -81,7 +81,9 @@ CoarseDims coarse_dims(int B, int N0, int N1, int C, int cand_per_row, int num_s
     d.N0pad = d.MT * kTileM;
     d.N1pad = d.NB * kBlockN;
     if (num_sms < 1) num_sms = 148;
-    const double ovh = 1.0;
+    // cost of a unit boundary in tiles: new resident block + column-sum reduction = 3 300 of a tile's 3 850 cycles,
+    // plus the pipeline refill (r02 timeline, tools/dbg_k1_trace.py); 1.0 under-counted it and chose too many units
+    const double ovh = 2.5;
     double best = 1e300;
     int best_tps = d.MT;
     int prev_tps = -1;
