@@ -199,7 +199,6 @@ __device__ __forceinline__ void emit_row(const CoarseResolveParams& p, int r, in
 //   3  per-block sums of the rows' match counts (rows in contiguous ranges, one range per block)
 //   4  exclusive offsets (every block adds up the sums before it) -> matches written in torch.where order
 constexpr int kResolveThreads = 512;
-constexpr int kCandUnroll = 4;
 
 struct ResolveWs {
     const uint2* meta; const float* dots; const int* hot_count;
