@@ -18,6 +18,7 @@ MAX_CHUNKS = 64
 ST_COUNT, ST_FLAGS, ST_MAX_CAND, ST_LOST, ST_CAND_TOTAL, ST_REDO = 0, 1, 2, 3, 4, 5
 FLAG_CAND_OVERFLOW, FLAG_OUT_OVERFLOW, FLAG_TIE_OVERFLOW, FLAG_RANGE = 1, 2, 4, 8
 POSE_POLISH, POSE_IDENTITY_K = 1, 2
+POSE_STATIC_SCRATCH_BYTES = 2 * 1024 * 1024
 
 _c = ctypes
 _P, _I, _F, _Z = _c.c_void_p, _c.c_int, _c.c_float, _c.c_size_t
@@ -52,6 +53,8 @@ SIGNATURES = {
     "fm_pose_workspace_bytes": (_Z, [_I, _I, _I]),
     "fm_pose_from_matches": (_I, [_P, _P, _P, _I, _P, _I, _I, _P, _F, _I, _I, _c.c_uint32, _P, _P, _P, _P, _P, _P, _P,
                                   _Z, _P]),
+    "fm_pose_from_matches_static": (_I, [_P, _P, _P, _I, _P, _I, _I, _P, _F, _I, _I, _c.c_uint32, _P, _P, _P, _P, _P, _P,
+                                         _P]),
     "fm_fine_match": (_I, [_P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _P, _P]),
 }
 

@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfm_b200.so")
 SOURCES = ["fm_api.cu", "coarse_prep.cu", "coarse_stats_tc.cu", "coarse_stats_simt.cu",
-           "coarse_resolve.cu", "fine_gather.cu", "fine_gather_tc.cu", "fine_match.cu", "fine_transformer.cu", "coarse_transformer.cu", "pose_ransac.cu",
+           "coarse_resolve.cu", "fine_gather.cu", "fine_gather_tc.cu", "fine_match.cu", "fine_transformer.cu", "coarse_transformer.cu", "pose_ransac.cu", "pose_static.cu",
            "backbone_emit.cu"]
 HEADERS = ["fm_common.cuh", "fm_ptx.cuh", "fm_tmap.cuh", "fm_tf_math.cuh", "fm_pose_math.cuh", os.path.join("..", "..", "include", "fm_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

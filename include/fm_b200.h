@@ -275,6 +275,29 @@ FM_API int fm_pose_from_matches(const int64_t* b_ids, const float* mkpts0_f, con
                                 int32_t* n_inliers, int32_t* pose_status, uint8_t* inlier_mask, void* workspace,
                                 size_t workspace_bytes, void* stream);
 
+/* Pose from matches without a caller-provided workspace.  No counterpart in the reference (its pose step is a host-side
+ * OpenCV call, pose_pred.py:130-151, which has no device scratch to speak of): this entry point exists for hosts of
+ * THIS library that cannot allocate device memory where they need a pose -- a plug-in in a serving process whose
+ * memory arena belongs to the framework, a per-frame callback of a live tracker where allocation latency is not
+ * allowed, a bare cgo / JNI / C binding that has no allocator at all.  Arguments, outputs, status codes and results are
+ * those of fm_pose_from_matches (same kernels, bit-identical output for the same inputs and seed); the intermediate
+ * buffers live in an array of FM_POSE_STATIC_SCRATCH_BYTES that is part of the library image on every GPU that loads
+ * it, for the life of the process.
+ *   - Limit: fm_pose_workspace_bytes(B, capacity, num_hypotheses) <= FM_POSE_STATIC_SCRATCH_BYTES (e.g. 8 pairs x 4096
+ *     hypotheses x 32768 matches); anything larger returns FM_ERR_WORKSPACE and names the size it would have needed.
+ *   - The call allocates nothing: no cudaMalloc / cudaFree / allocating library routine, ever.
+ *   - The first call on each device resolves the array's device address (not stream work; it may load a module):
+ *     make it at start-up, before any stream capture begins.  Later calls only enqueue kernels on `stream`.
+ *   - One array per device, shared by all threads and streams: calls that can overlap on the GPU race on it and
+ *     return garbage -- keep them on one stream or order them with events.  Contents left by an earlier call are
+ *     harmless (every word is rewritten before it is read). */
+#define FM_POSE_STATIC_SCRATCH_BYTES (2 * 1024 * 1024)
+FM_API int fm_pose_from_matches_static(const int64_t* b_ids, const float* mkpts0_f, const float* mkpts1_f,
+                                       int pts_stride, const int32_t* count, int capacity, int B, const float* K0,
+                                       float threshold_px, int num_hypotheses, int flags, uint32_t seed, float* R,
+                                       float* t, float* E, int32_t* n_inliers, int32_t* pose_status,
+                                       uint8_t* inlier_mask, void* stream);
+
 /* ---------------------------------------------------------------- test / profiling hooks
  * Same contract as fm_coarse_match, but the score statistics come from a plain SIMT kernel
  * instead of the tcgen05 kernel.  Exists so tests can tell a tensor-core plumbing bug from a
