@@ -175,7 +175,9 @@ def fine_transformer_module():
     import torch
     from featurematching_b200 import modules
     torch.manual_seed(77)
-    return modules.LocalFeatureTransformer(FINE_CFG).eval()
+    m = modules.LocalFeatureTransformer(FINE_CFG).eval()
+    m.reuse_packed_weights = True   # the bench owns these weights and never writes them: pack once (eval-mode serving)
+    return m
 
 
 def coarse_transformer_module():
@@ -183,7 +185,9 @@ def coarse_transformer_module():
     import torch
     from featurematching_b200 import modules
     torch.manual_seed(78)
-    return modules.LocalFeatureTransformer(COARSE_CFG).eval()
+    m = modules.LocalFeatureTransformer(COARSE_CFG).eval()
+    m.reuse_packed_weights = True
+    return m
 
 
 def oracle_head(args, device="cpu"):

@@ -62,6 +62,20 @@ class CoarseRaw:
     __slots__ = ("b_ids", "i_ids", "j_ids", "mconf", "mkpts0_c", "mkpts1_c", "status", "capacity")
 
 
+def _bf16_twin(feat):
+    """The bf16 rounding the B200 coarse transformer attached to the fp32 tokens it returned (`_fm_bf16` = (tensor,
+    version of the fp32 tokens at that moment)), or None.  An in-place edit of the fp32 tokens after the transformer
+    (masking, `mul_`, `feat[...] = 0`, a user hook) bumps their version: the twin is stale then and the caller casts
+    the edited tokens itself."""
+    twin = getattr(feat, "_fm_bf16", None)
+    if twin is None:
+        return None
+    t, version = twin
+    if version != feat._version or t.shape != feat.shape or t.device != feat.device:
+        return None
+    return t
+
+
 class CoarseMatching(nn.Module):
     """network/utils/coarse_matching_new.py:30-143 on the fused tcgen05 kernel."""
 
@@ -85,9 +99,8 @@ class CoarseMatching(nn.Module):
         _require_cuda(feat_c0, feat_c1)
         # tokens that come out of the B200 coarse transformer carry their bf16 rounding (written by the
         # transformer's last epilogue, bit-equal to rn(fp32)): use it instead of casting again
-        b0, b1 = getattr(feat_c0, "_fm_bf16", None), getattr(feat_c1, "_fm_bf16", None)
-        if (b0 is not None and b1 is not None and b0.shape == feat_c0.shape and b1.shape == feat_c1.shape
-                and b0.device == feat_c0.device):
+        b0, b1 = _bf16_twin(feat_c0), _bf16_twin(feat_c1)
+        if b0 is not None and b1 is not None:
             feat_c0, feat_c1 = b0, b1
         f0, f1 = _feat(feat_c0), _feat(feat_c1)
         if f0.dtype != f1.dtype:
@@ -245,9 +258,8 @@ class FinePreprocess(nn.Module):
             _require_cuda(feat_c0, feat_c1)
             # the window-context GEMM reads the tokens in bf16, like the coarse contraction: take the rounding the
             # B200 coarse transformer already wrote (bit-equal to the cast the kernel would do itself)
-            t0, t1 = getattr(feat_c0, "_fm_bf16", None), getattr(feat_c1, "_fm_bf16", None)
-            if (t0 is not None and t1 is not None and t0.shape == feat_c0.shape and t1.shape == feat_c1.shape
-                    and t0.device == feat_c0.device):
+            t0, t1 = _bf16_twin(feat_c0), _bf16_twin(feat_c1)
+            if t0 is not None and t1 is not None:
                 feat_c0, feat_c1 = t0, t1
             c0, c1 = _feat(feat_c0), _feat(feat_c1)
             if c0.dtype != c1.dtype:
@@ -402,7 +414,32 @@ class LocalFeatureTransformer(nn.Module):
         self.layers = nn.ModuleList([EncoderLayer(self.d_model, self.nhead)
                                      for _ in self.layer_names])
         self._ws = _Workspace()
+        # Eval-mode shortcut, OFF unless the owner of the weights turns it on: keep the operand-form copy of the
+        # weights in the workspace across calls instead of re-packing them on every call.  Staleness is detected
+        # through the parameters' storages and autograd versions, which `load_state_dict`, `.to()`, optimiser steps
+        # and `p.mul_()` change -- but writes through `p.data` (EMA swaps, hand-written checkpoint loaders) do NOT:
+        # after such a write call invalidate_packed(), or leave the shortcut off.
+        self.reuse_packed_weights = False
+        self._packed_key = None
+        self._packed_event = None
         self._reset_parameters()
+
+    def invalidate_packed(self):
+        """Forget the packed weights: the next call re-packs from the parameters as they are then."""
+        self._packed_key = None
+        self._packed_event = None
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        self.invalidate_packed()
+        return super()._load_from_state_dict(*args, **kwargs)
+
+    def _apply(self, fn, *args, **kwargs):
+        self.invalidate_packed()
+        return super()._apply(fn, *args, **kwargs)
+
+    def train(self, mode=True):
+        self.invalidate_packed()
+        return super().train(mode)
 
     def _reset_parameters(self):   # transformer.py:73-76
         for p in self.parameters():
@@ -410,10 +447,9 @@ class LocalFeatureTransformer(nn.Module):
                 nn.init.xavier_uniform_(p)
 
     def _layer_args(self, dev, ws):
-        """(n, kinds, ptrs, keepalive): ctypes arguments of the layers' parameters.  `ptrs` is None when `ws` (the
-        workspace tensor) already holds these very parameters in packed form: same workspace storage, same
-        parameter storages and versions as the previous call -- the eval-mode case, where re-packing 0.65 M weights
-        per layer on every call is wasted work."""
+        """(n, kinds, ptrs, keepalive): ctypes arguments of the layers' parameters.  With `reuse_packed_weights` on,
+        `ptrs` is None when `ws` (the workspace tensor) already holds these very parameters in packed form: same
+        workspace storage, same parameter storages and versions as the previous call, no invalidate_packed() since."""
         import ctypes
         n = len(self.layers)
         params = [t.detach().to(device=dev, dtype=torch.float32).contiguous()
@@ -421,10 +457,19 @@ class LocalFeatureTransformer(nn.Module):
         key = (ws.data_ptr(), tuple((t.data_ptr(), t._version) for layer in self.layers for t in layer.flat_parameters()),
                tuple(t.data_ptr() for t in params))
         kinds = (ctypes.c_int32 * n)(*[0 if k == 'self' else 1 for k in self.layer_names])
-        if getattr(self, "_packed_key", None) == key:
+        if self.reuse_packed_weights and self._packed_key == key:
+            # the packing was enqueued on the stream of that earlier call: a call on another stream waits for it
+            if self._packed_event is not None and ws.is_cuda:
+                torch.cuda.current_stream(ws.device).wait_event(self._packed_event)
             return n, kinds, None, params
-        self._packed_key = key
+        self._packed_key = key if self.reuse_packed_weights else None
+        self._packed_event = None
         return n, kinds, (ctypes.c_void_p * (10 * n))(*[t.data_ptr() for t in params]), params
+
+    def _mark_packed(self, ptrs, dev):
+        if ptrs is not None and self._packed_key is not None:
+            self._packed_event = torch.cuda.Event()
+            self._packed_event.record(torch.cuda.current_stream(dev))
 
     def transform(self, feat0, feat1, count=None, out=None):
         """Device-side call: [cap, WW, C] fp32 windows -> updated windows (`out` may be the
@@ -448,6 +493,7 @@ class LocalFeatureTransformer(nn.Module):
         if rc != 0:
             self._packed_key = None
         _lib.check(rc, "fm_fine_transformer")
+        self._mark_packed(ptrs, dev)
         self._keepalive = params   # the launch is asynchronous
         return o0, o1
 
@@ -476,6 +522,7 @@ class LocalFeatureTransformer(nn.Module):
         if rc != 0:
             self._packed_key = None
         _lib.check(rc, "fm_coarse_transformer")
+        self._mark_packed(ptrs, dev)
         self._keepalive = params   # the launch is asynchronous
         return o0, o1
 
@@ -491,7 +538,9 @@ class LocalFeatureTransformer(nn.Module):
                 b = (torch.empty(feat0.shape, dtype=torch.bfloat16, device=feat0.device),
                      torch.empty(feat1.shape, dtype=torch.bfloat16, device=feat1.device))
                 o0, o1 = self.transform_tokens(feat0, feat1, bf16_out=b)
-                o0._fm_bf16, o1._fm_bf16 = b   # CoarseMatching.match_raw picks these up (no second cast pass)
+                # CoarseMatching.match_raw / FinePreprocess pick these up (no second cast pass) for as long as the
+                # fp32 tokens keep the version they have now (_bf16_twin)
+                o0._fm_bf16, o1._fm_bf16 = (b[0], o0._version), (b[1], o1._version)
                 return o0, o1
             return self.transform(feat0, feat1)
 

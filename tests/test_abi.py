@@ -202,3 +202,48 @@ def test_backbone_emit_argument_errors(lib):
     assert call(rows=0) == 0                                                  # nothing to do
     if not torch.cuda.is_available():
         assert call() == -3 and call(Cin=128, Cout=256) == -3                 # FM_ERR_CUDA: no CPU path
+
+
+def test_packed_weight_cache_is_opt_in_and_invalidated_on_cpu():
+    """Host logic of LocalFeatureTransformer's packed-weight shortcut (ADVICE r02), no kernels involved: off by default;
+    when on, the second call passes layer_params = NULL; tracked in-place updates, invalidate_packed(),
+    load_state_dict, train() and _apply (.to / .float) all force a re-pack."""
+    from featurematching_b200 import modules
+    m = modules.LocalFeatureTransformer({"d_model": 64, "nhead": 8, "layer_names": ["self", "cross"], "attention": "linear"}).eval()
+    ws = torch.empty(64, dtype=torch.uint8)
+    cpu = torch.device("cpu")
+    assert m.reuse_packed_weights is False
+    for _ in range(2):
+        n, kinds, ptrs, keep = m._layer_args(cpu, ws)
+        assert n == 2 and list(kinds) == [0, 1] and ptrs is not None and len(ptrs) == 20 and m._packed_key is None
+    m.reuse_packed_weights = True
+    assert m._layer_args(cpu, ws)[2] is not None
+    assert m._layer_args(cpu, ws)[2] is None                   # same workspace, same parameters: reuse
+    assert m._layer_args(cpu, torch.empty(64, dtype=torch.uint8))[2] is not None   # another workspace
+    m._layer_args(cpu, ws)
+    with torch.no_grad():
+        m.layers[1].merge.weight.mul_(2.0)                     # version bump
+    assert m._layer_args(cpu, ws)[2] is not None
+    m.layers[0].norm1.bias.data.add_(1.0)                      # .data write: invisible to the key ...
+    assert m._layer_args(cpu, ws)[2] is None
+    m.invalidate_packed()                                      # ... so the owner says so
+    assert m._layer_args(cpu, ws)[2] is not None
+    for poke in (lambda: m.load_state_dict(m.state_dict()), lambda: m.train(False), lambda: m.float()):
+        assert m._layer_args(cpu, ws)[2] is None
+        poke()
+        assert m._layer_args(cpu, ws)[2] is not None
+
+
+def test_bf16_twin_is_dropped_after_an_in_place_edit():
+    """The bf16 rounding the coarse transformer hangs on its fp32 output is only valid for the version of the tokens
+    it was made from: an in-place edit in between makes the matcher cast the edited tokens itself."""
+    from featurematching_b200 import modules
+    tok = torch.randn(1, 12, 256)
+    twin = tok.to(torch.bfloat16)
+    assert modules._bf16_twin(tok) is None
+    tok._fm_bf16 = (twin, tok._version)
+    assert modules._bf16_twin(tok) is twin
+    tok[:, 3] = 0                                              # masking after the transformer
+    assert modules._bf16_twin(tok) is None
+    tok._fm_bf16 = (twin[:, :5], tok._version)                 # wrong shape: ignored as before
+    assert modules._bf16_twin(tok) is None

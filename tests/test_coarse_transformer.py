@@ -115,6 +115,40 @@ def test_coarse_transformer_is_deterministic():
 
 
 @pytest.mark.gpu
+def test_in_place_edit_after_the_transformer_reaches_the_matcher():
+    """The transformer hangs the bf16 rounding of its tokens on the fp32 tensors it returns; the coarse matcher uses it
+    only while the fp32 tokens are untouched.  Zeroing a block of tokens in place in between (what a mask or a user hook
+    in an install()ed net does) must change the matches exactly as if the matcher had been given plain tensors."""
+    from featurematching_b200 import modules
+    names = ["self", "cross"]
+    layers = mo.seeded_transformer_layers(7, 256, 2)
+    f0, _ = mo.seeded_tokens(8, 1, 320, 320, 256)
+    m = _module(layers, names, "cuda")
+    cm = modules.CoarseMatching({"thr": 0.2, "border_rm": 0, "dsmax_temperature": 0.1}).eval()
+    shape = {"hw0_i": (128, 160), "hw0_c": (16, 20), "hw1_c": (16, 20)}
+
+    def ids(a, b):
+        d = dict(shape)
+        cm(a, b, d)
+        return d["i_ids"].clone(), d["j_ids"].clone()
+
+    # identical images: the same tokens on both sides give a diagonal of confident matches
+    o0, o1 = m(f0.cuda(), f0.cuda())
+    assert modules._bf16_twin(o0) is not None and modules._bf16_twin(o1) is not None
+    scale = 24.0 / o0.norm(dim=-1, keepdim=True)
+    o0.mul_(scale); o1.mul_(scale)              # an in-place edit already: the twins are stale from here on
+    assert modules._bf16_twin(o0) is None and modules._bf16_twin(o1) is None
+    before = ids(o0, o1)
+    assert before[0].numel() > 100
+    o0[:, 100:200] = 0                           # mask a block of image-0 tokens
+    after = ids(o0, o1)
+    plain = ids(o0.clone(), o1.clone())          # clones carry no twin at all
+    assert torch.equal(after[0], plain[0]) and torch.equal(after[1], plain[1])
+    assert after[0].numel() < before[0].numel()
+    assert not ((after[0] >= 100) & (after[0] < 200)).any()
+
+
+@pytest.mark.gpu
 def test_coarse_transformer_rejects_unsupported():
     from featurematching_b200 import _lib, modules
     m = modules.LocalFeatureTransformer({"d_model": 256, "nhead": 4, "layer_names": ["self"], "attention": "linear"}).cuda().eval()

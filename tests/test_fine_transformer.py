@@ -252,8 +252,10 @@ def test_chain_with_transformer_kernels_match_reference_golden(golden_dir):
 
 @pytest.mark.gpu
 def test_packed_weights_are_reused_and_invalidated():
-    """Eval-mode calls reuse the weights packed into the module's workspace (layer_params = NULL through the C ABI);
-    an in-place parameter update or a new workspace forces a re-pack."""
+    """With reuse_packed_weights on, eval-mode calls reuse the weights packed into the module's workspace
+    (layer_params = NULL through the C ABI); a tracked in-place update forces a re-pack, and so does
+    invalidate_packed() after a write through `.data` (which no version counter sees).  With the switch off (the
+    default) a `.data` write is picked up by the next call without further ado."""
     import torch
     from featurematching_b200 import modules
     from oracle import matcher_oracle as mo
@@ -261,17 +263,50 @@ def test_packed_weights_are_reused_and_invalidated():
     names = ["self", "cross"]
     m = modules.LocalFeatureTransformer({"d_model": 64, "nhead": 8, "layer_names": names, "attention": "linear"}).eval().cuda()
     x0, x1 = torch.randn(37, 49, 64), torch.randn(37, 49, 64)
+
+    def oracle():
+        layers = mo.transformer_params_from_state_dict({k: v.cpu() for k, v in m.state_dict().items()}, len(names))
+        return mo.local_feature_transformer(x0, x1, layers, names, 8)
+
+    def close(g, r):
+        return (g[0].cpu() - r[0]).abs().max() < 2e-4 and (g[1].cpu() - r[1]).abs().max() < 2e-4
+
+    # default: no reuse, a write through .data shows in the very next call
+    assert m.reuse_packed_weights is False
+    d0 = m(x0.cuda(), x1.cuda())
+    assert m._packed_key is None and close(d0, oracle())
+    m.layers[0].k_proj.weight.data.copy_(m.layers[0].k_proj.weight.data * 0.5)
+    d1 = m(x0.cuda(), x1.cuda())
+    assert close(d1, oracle()) and (d1[0] - d0[0]).abs().max() > 1e-3
+
+    m.reuse_packed_weights = True
     a0, a1 = m(x0.cuda(), x1.cuda())
-    assert m._packed_key is not None
+    assert m._packed_key is not None and m._packed_event is not None
     key = m._packed_key
     b0, b1 = m(x0.cuda(), x1.cuda())             # second call: packing skipped
     assert m._packed_key == key
     assert torch.equal(a0, b0) and torch.equal(a1, b1)
+    side = torch.cuda.Stream()                    # a reusing call on another stream waits for the packing call
+    with torch.cuda.stream(side):
+        s0, s1 = m(x0.cuda(), x1.cuda())
+    side.synchronize()
+    assert torch.equal(a0, s0) and torch.equal(a1, s1)
     with torch.no_grad():
         m.layers[0].q_proj.weight.mul_(0.5)      # in-place update bumps the version: must re-pack
     c0, c1 = m(x0.cuda(), x1.cuda())
     assert m._packed_key != key
-    layers = mo.transformer_params_from_state_dict({k: v.cpu() for k, v in m.state_dict().items()}, len(names))
-    r0, r1 = mo.local_feature_transformer(x0, x1, layers, names, 8)
-    assert (c0.cpu() - r0).abs().max() < 2e-4 and (c1.cpu() - r1).abs().max() < 2e-4
+    assert close((c0, c1), oracle())
     assert (c0 - a0).abs().max() > 1e-3          # and the result did change
+    # a write through .data is invisible to the key: stale until the owner says so
+    m.layers[1].norm2.weight.data.copy_(m.layers[1].norm2.weight.data * 3.0)
+    stale = m(x0.cuda(), x1.cuda())
+    assert torch.equal(stale[0], c0)
+    m.invalidate_packed()
+    fresh = m(x0.cuda(), x1.cuda())
+    assert close(fresh, oracle()) and (fresh[0] - c0).abs().max() > 1e-3
+    # load_state_dict / train() / .to() invalidate on their own
+    for poke in (lambda: m.load_state_dict(m.state_dict()), lambda: m.train(False), lambda: m.to("cuda")):
+        m(x0.cuda(), x1.cuda())
+        assert m._packed_key is not None
+        poke()
+        assert m._packed_key is None
