@@ -277,8 +277,11 @@ def parity_check(args, inp, ref, gpu0):
     ties = 0
     if diff:
         o64 = mo.coarse_match(inp[0], inp[1], hw_i, hw_c, hw_c, dtype=torch.float64, return_conf=True)["conf_matrix"]
-        ties = sum(1 for (a, b) in diff if compare._ambiguous(o64, 0, a, b, 0.2))
+        ties = sum(1 for (a, b) in diff if compare._ambiguous(o64, 0, a, b, HEAD_CFG["match_coarse"]["thr"]))
     common = sorted(so & sr)
+    if not common:   # nothing to compare coordinates on: that is a failed check, not a crash
+        return {"parity_checked": True, "parity_ok": False, "pair": 0, "matches_gpu": len(so), "matches_oracle": len(sr),
+                "id_differences": len(diff), "of_which_fp64_ties": ties, "note": "GPU and oracle share no match"}
     io = {t: k for k, t in enumerate(zip(ours["i_ids"].tolist(), ours["j_ids"].tolist()))}
     ir = {t: k for k, t in enumerate(zip(ref["i_ids"].tolist(), ref["j_ids"].tolist()))}
     ko, kr = torch.tensor([io[t] for t in common]), torch.tensor([ir[t] for t in common])
@@ -287,10 +290,16 @@ def parity_check(args, inp, ref, gpu0):
              float((mk1[ko][:, :2].double() - ref["mkpts1_f"][kr][:, :2].double()).abs().max()))
     std_rel = max(float(((mk0[ko][:, 2].double() - ref["mkpts0_f"][kr][:, 2].double()).abs() / (ref["mkpts0_f"][kr][:, 2].double().abs() + 1e-2)).max()),
                   float(((mk1[ko][:, 2].double() - ref["mkpts1_f"][kr][:, 2].double()).abs() / (ref["mkpts1_f"][kr][:, 2].double().abs() + 1e-2)).max()))
-    ok = (len(diff) == ties) and conf_rel <= compare.CONF_RTOL and px <= compare.COORD_TOL_PX
+    # the std bar of oracle/compare.py: |err| <= STD_ATOL + STD_RTOL * |ref|; reported as the worst ratio
+    std_bar = 0.0
+    for o, r in ((mk0[ko][:, 2], ref["mkpts0_f"][kr][:, 2]), (mk1[ko][:, 2], ref["mkpts1_f"][kr][:, 2])):
+        std_bar = max(std_bar, float(((o.double() - r.double()).abs() / (compare.STD_ATOL + compare.STD_RTOL * r.double().abs())).max()))
+    ok = (len(diff) == ties) and conf_rel <= compare.CONF_RTOL and px <= compare.COORD_TOL_PX and std_bar <= 1.0
     return {"parity_checked": True, "parity_ok": bool(ok), "pair": 0, "matches_gpu": len(so), "matches_oracle": len(sr),
             "id_differences": len(diff), "of_which_fp64_ties": ties, "max_conf_rel_err": conf_rel, "max_px_err": px,
-            "max_std_rel_err": std_rel, "bars": {"conf_rel": compare.CONF_RTOL, "px": compare.COORD_TOL_PX}}
+            "max_std_rel_err": std_rel, "max_std_err_over_bar": std_bar,
+            "bars": {"conf_rel": compare.CONF_RTOL, "px": compare.COORD_TOL_PX, "std_rel": compare.STD_RTOL,
+                     "std_abs": compare.STD_ATOL}}
 
 
 def run_reference(args):

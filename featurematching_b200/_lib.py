@@ -53,6 +53,7 @@ SIGNATURES = {
     "fm_pose_workspace_bytes": (_Z, [_I, _I, _I]),
     "fm_pose_from_matches": (_I, [_P, _P, _P, _I, _P, _I, _I, _P, _F, _I, _I, _c.c_uint32, _P, _P, _P, _P, _P, _P, _P,
                                   _Z, _P]),
+    "fm_debug_pose_valid_hypotheses": (_I, [_P, _I, _I, _I, _P, _P]),
     "fm_pose_from_matches_static": (_I, [_P, _P, _P, _I, _P, _I, _I, _P, _F, _I, _I, _c.c_uint32, _P, _P, _P, _P, _P, _P,
                                          _P]),
     "fm_fine_match": (_I, [_P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _P, _P]),

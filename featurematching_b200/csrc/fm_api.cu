@@ -200,6 +200,8 @@ cudaError_t launch_pose_from_matches(const int64_t* b_ids, const float* mk0, con
                                      float* R, float* t, float* E, int* n_inliers, int* status, uint8_t* mask,
                                      void* workspace, cudaStream_t st);
 
+cudaError_t launch_pose_count_valid(const void* workspace, int B, int capacity, int H, int* valid, cudaStream_t st);
+
 static bool dtype_ok(int t) { return t == FM_DTYPE_BF16 || t == FM_DTYPE_F32; }
 
 static int check_coarse_args(const void* f0, const void* f1, int dt, int B, int N0, int N1, int C, int h0c, int w0c,
@@ -618,6 +620,18 @@ int fm_pose_from_matches(const int64_t* b_ids, const float* mkpts0_f, const floa
                                              num_hypotheses, flags, seed, R, t, E, n_inliers, pose_status, inlier_mask,
                                              workspace, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return cuda_fail(e, "pose_from_matches launch");
+    return FM_OK;
+}
+
+int fm_debug_pose_valid_hypotheses(const void* workspace, int B, int capacity, int num_hypotheses, int32_t* valid,
+                                   void* stream) {
+    if (!workspace || !valid || B < 1 || capacity < 0 || num_hypotheses < 1 || num_hypotheses > (1 << 20)) {
+        set_error("bad argument to fm_debug_pose_valid_hypotheses");
+        return FM_ERR_BAD_ARG;
+    }
+    if (sm_count() <= 0) { set_error("no CUDA device available (this library has no CPU path)"); return FM_ERR_CUDA; }
+    cudaError_t e = launch_pose_count_valid(workspace, B, capacity, num_hypotheses, valid, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "pose_count_valid launch");
     return FM_OK;
 }
 

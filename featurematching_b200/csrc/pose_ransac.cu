@@ -421,16 +421,44 @@ __global__ void __launch_bounds__(kPoseThreads) pose_finalize_kernel(PoseParams 
     if (threadIdx.x == 0) {
         const int c = best_candidate(good);
         const double* Rs = s_R[c & 1];
-        for (int i = 0; i < 9; ++i) { R[i] = static_cast<float>(Rs[i]); if (p.E) p.E[9 * b + i] = E[i]; }
-        for (int i = 0; i < 3; ++i) t[i] = static_cast<float>((c & 2) ? tn[i] : tp[i]);
+        // no inlier in front of both cameras under any of the four candidates: recoverPose returns n = 0, the
+        // reference's `n > best_num_inliers` never holds and it hands back None (pose_pred.py:143-151) -> R = I, t = 0;
+        // E, the inlier count and the mask stay (they describe the model that was found)
+        const bool none_in_front = good[c] == 0;
+        for (int i = 0; i < 9; ++i) {
+            R[i] = none_in_front ? ((i % 4 == 0) ? 1.f : 0.f) : static_cast<float>(Rs[i]);
+            if (p.E) p.E[9 * b + i] = E[i];
+        }
+        for (int i = 0; i < 3; ++i) t[i] = none_in_front ? 0.f : static_cast<float>((c & 2) ? tn[i] : tp[i]);
         p.n_inliers[b] = ninl;
-        p.status[b] = 0;
+        p.status[b] = none_in_front ? 3 : 0;
     }
+}
+
+// ---- debug: how many of a pair's H samples produced a model (pose_hypotheses_kernel marks the others with E[0] = NaN).
+// Reads the workspace a finished fm_pose_from_matches call left behind; pairs with fewer than 8 matches report 0.
+__global__ void __launch_bounds__(kPoseThreads) pose_count_valid_kernel(PoseWs w, int H, int* valid) {
+    __shared__ int s_cnt[kPoseThreads / 32];
+    const int b = blockIdx.x;
+    int c = 0;
+    if (w.range[b + 1] - w.range[b] >= 8)
+        for (int h = threadIdx.x; h < H; h += kPoseThreads) {
+            const float e0 = w.hyp[(static_cast<size_t>(b) * H + h) * 9];
+            c += (e0 == e0) ? 1 : 0;
+        }
+    c = block_sum_int(c, s_cnt);
+    if (threadIdx.x == 0) valid[b] = c;
 }
 
 }  // namespace
 
 size_t pose_workspace_bytes(int B, int capacity, int H) { return carve(B, capacity, H, nullptr).total; }
+
+cudaError_t launch_pose_count_valid(const void* workspace, int B, int capacity, int H, int* valid, cudaStream_t st) {
+    const PoseWs w = carve(B, capacity, H, const_cast<void*>(workspace));
+    pose_count_valid_kernel<<<B, kPoseThreads, 0, st>>>(w, H, valid); count_launch();
+    return cudaGetLastError();
+}
 
 cudaError_t launch_pose_from_matches(const int64_t* b_ids, const float* mk0, const float* mk1, int stride, const int* count,
                                      int capacity, int B, const float* K, float thr_px, int H, int flags, uint32_t seed,

@@ -35,7 +35,9 @@ class PoseFromMatches:
         """b_ids int64 [cap] sorted; mkpts*_f float32 [cap, 2 or 3]; K0 [num_pairs, 3, 3]; count = device int32
         match count for padded buffers.  Enqueues on the current stream, no host synchronisation.  Returns a dict of
         device tensors: R [B, 3, 3], t [B, 3], E [B, 3, 3], n_inliers [B], status [B] (0 ok, 1 = fewer than 8
-        matches, 2 = no model; R = I, t = 0 then, like pose_pred.py:177-179) and inlier_mask uint8 [cap]."""
+        matches, 2 = no model, 3 = no inlier in front of both cameras, recoverPose's n = 0; R = I, t = 0 for 1-3, like
+        pose_pred.py:177-179) and inlier_mask uint8 [cap].  The reference's 5-point solver also answers 5-7 matches;
+        here those pairs are status 1."""
         lib = _lib.load()
         for t_ in (b_ids, mkpts0_f, mkpts1_f, K0):
             if not t_.is_cuda:
@@ -74,6 +76,18 @@ class PoseFromMatches:
             out["inlier_mask"] = out["inlier_mask"][:cap]
         return out
 
+    def valid_hypotheses(self, num_pairs, capacity):
+        """Debug: int32 [num_pairs] = how many of the samples of the LAST estimate() call (same num_pairs and capacity)
+        gave a model.  Reads the workspace that call left behind."""
+        lib = _lib.load()
+        dev = self._ws.device
+        out = torch.empty(int(num_pairs), dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.fm_debug_pose_valid_hypotheses(_lib.ptr(self._ws), int(num_pairs), int(capacity), self.num_hypotheses,
+                                                    _lib.ptr(out), _lib.stream_ptr(dev))
+        _lib.check(rc, "fm_debug_pose_valid_hypotheses")
+        return out
+
     def estimate_from_data(self, data):
         """`data` as net.forward leaves it (m_bids, mkpts0_f, mkpts1_f) plus data['K0'] [bs, 3, 3]: one pose per
         batch element, the loop of utils/metrics.py:146-159 in one call.  Writes data['R_pred'], ['t_pred'],
@@ -101,7 +115,7 @@ def get_opencv_pose(data, solver=None):
     solver = solver or PoseFromMatches()
     dev = data['mkpts0_f'].device
     M = data['mkpts0_f'].shape[0]
-    if M < 5:   # pose_pred.py:131-132
+    if M < 5:   # pose_pred.py:131-132 (5 <= M < 8 also ends as R = I, t = 0: status 1 of the 8-point solver)
         R = torch.eye(3, device=dev)[None]
         t = torch.zeros(1, 3, device=dev)
     else:

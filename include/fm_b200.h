@@ -263,8 +263,11 @@ FM_API int fm_backbone_emit(const float* x, long long rows, int Cin, int Cout, c
  *                              exactly as the reference's recoverPose call does; without it the normalised
  *                              coordinates are used (what cv2.recoverPose(E, p0, p1, K) computes)
  * Outputs per pair: R float[B, 9] row-major, t float[B, 3] unit vector, E float[B, 9] (may be NULL), n_inliers,
- * pose_status (0 = ok, 1 = fewer than 8 matches, 2 = no sample gave a model; R = I, t = 0 for 1 and 2) and,
- * if not NULL, inlier_mask uint8[capacity] aligned with the match list.
+ * pose_status (0 = ok, 1 = fewer than 8 matches, 2 = no sample gave a model, 3 = a model was found but no inlier
+ * triangulates in front of both cameras -- recoverPose's n = 0, the reference's None; R = I, t = 0 for 1, 2 and 3)
+ * and, if not NULL, inlier_mask uint8[capacity] aligned with the match list.
+ * Known difference: the reference's 5-point solver also answers pairs with 5, 6 or 7 matches; this 8-point solver
+ * reports them as status 1 (identity pose), like pairs with fewer than 5.
  * workspace: fm_pose_workspace_bytes(B, capacity, num_hypotheses) bytes, 16-byte aligned. */
 #define FM_POSE_POLISH 1
 #define FM_POSE_IDENTITY_K 2
@@ -314,6 +317,13 @@ FM_API int fm_debug_coarse_match_simt(const void* feat_c0, const void* feat_c1, 
  * l2row float[B*N0], l2col float[B*N1] (device pointers). */
 FM_API int fm_debug_coarse_lse(const void* workspace, int B, int N0, int N1, int C, int feat_dtype,
                         int cand_per_row, float* l2row, float* l2col, void* stream);
+
+/* Number of hypotheses per pair that produced a model in the fm_pose_from_matches call that last used `workspace`
+ * (same B, capacity, num_hypotheses): valid int32[B], 0 for pairs with fewer than 8 matches.  A healthy build turns
+ * nearly every sample of a non-degenerate pair into a model; tests assert that (a miscompiled null-space routine once
+ * rejected every sample and the API answered with identity poses, status 2). */
+FM_API int fm_debug_pose_valid_hypotheses(const void* workspace, int B, int capacity, int num_hypotheses,
+                                          int32_t* valid, void* stream);
 
 /* Times only the coarse statistics kernel (the tcgen05 GEMM + fused dual-softmax sums):
  * runs it `iters` times on `stream` and returns the mean milliseconds per launch in *ms. */

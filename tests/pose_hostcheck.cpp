@@ -118,6 +118,13 @@ extern "C" int pose_hostcheck(const float* k0, const float* k1, int M, const flo
         good[3] += in_front_of_both(R2, tn, a0, b0, a1, b1, 1e9);
     }
     const int c = best_candidate(good);
+    if (good[c] == 0) {   // recoverPose's n = 0: the reference returns None (pose_pred.py:143-151)
+        for (int i = 0; i < 9; ++i) { R_out[i] = (i % 4 == 0) ? 1.f : 0.f; E_out[i] = static_cast<float>(E[i]); }
+        for (int i = 0; i < 3; ++i) t_out[i] = 0.f;
+        *n_inliers = n;
+        std::memcpy(mask, inl.data(), M);
+        return 3;
+    }
     const double* R = (c & 1) ? R2 : R1;
     const double* tt = (c & 2) ? tn : t;
     for (int i = 0; i < 9; ++i) { R_out[i] = static_cast<float>(R[i]); E_out[i] = static_cast<float>(E[i]); }
