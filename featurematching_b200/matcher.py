@@ -20,6 +20,21 @@ from . import modules
 from .backbone import SwinUNetBackbone
 
 
+def default_config():
+    """The matcher hyper-parameters the reference ships (demo/net_config.py:8-46) as the lower-cased dict its modules
+    receive: the configuration `Matcher`, the bench and the demos run when no other is given."""
+    return {
+        "fine_window_size": 7,
+        "fine_concat_coarse_feat": True,
+        "coarse": {"d_model": 256, "nhead": 8, "layer_names": ["self", "cross"] * 4, "attention": "linear"},
+        "match_coarse": {"thr": 0.2, "border_rm": 2, "match_type": "dual_softmax", "dsmax_temperature": 0.1,
+                         "train_coarse_percent": 1.0, "train_pad_num_gt_min": 200},
+        "fine": {"d_model": 64, "nhead": 8, "layer_names": ["self", "cross"], "attention": "linear"},
+        "pose_net_flag": "none",
+        "backbone_type": "swin", "input_channel": 3, "resolution": (8, 2),
+    }
+
+
 class Matcher(nn.Module):
     def __init__(self, config, emit_bf16_fine=True):
         super().__init__()

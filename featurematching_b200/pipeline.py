@@ -382,11 +382,6 @@ class OverlappedGather:
         self.busy[s] = True
         return self.out
 
-    def before_pack(self):
-        """Kept for callers written against the single-buffer version: the caller's records buffer is never
-        held by an exchange any more, so this only makes sure a staged exchange has been enqueued."""
-        self.launch()
-
     def finish(self):
         """Sends what is staged and joins the side stream into the current one (device-side)."""
         self.launch()

@@ -67,9 +67,27 @@ def check_coarse(ours, ref, conf64=None, thr=0.2):
     return len(diff)
 
 
-def check_fine(ours0, ours1, ref0, ref1):
-    """[M, 3] = (x px, y px, std): coordinates within COORD_TOL_PX, std within STD_RTOL."""
-    for o, r in ((ours0, ref0), (ours1, ref1)):
+def common_rows(ours, ref):
+    """Row indices (into ours, into ref) of the matches both lists hold, keyed on (b, i, j): lets the fine columns be
+    compared when a tolerated tie made the two lists differ in a few entries."""
+    key = lambda d: list(zip(torch.as_tensor(d["b_ids"]).cpu().tolist(), torch.as_tensor(d["i_ids"]).cpu().tolist(),
+                             torch.as_tensor(d["j_ids"]).cpu().tolist()))
+    ko_map = {t: k for k, t in enumerate(key(ours))}
+    kr_map = {t: k for k, t in enumerate(key(ref))}
+    common = sorted(set(ko_map) & set(kr_map))
+    return (torch.tensor([ko_map[t] for t in common], dtype=torch.long),
+            torch.tensor([kr_map[t] for t in common], dtype=torch.long))
+
+
+def check_fine(ours0, ours1, ref0, ref1, std_ref0=None, std_ref1=None):
+    """[M, 3] = (x px, y px, std): coordinates within COORD_TOL_PX, std within STD_ATOL + STD_RTOL |std|.
+
+    std_ref0 / std_ref1 (optional [M, 3], the oracle evaluated in fp64): the std column is then compared with THESE.
+    The reference's std = sqrt(E[g^2] - E[g]^2) (fine_matching_new.py:69-73) cancels in fp32 when the heat map is
+    peaked -- at std ~ 0.006 the fp32 oracle itself sits 1e-3 relative from the exact value of its own formula and a
+    few matches per 18 000 land outside the bar through no fault of either side (tools/std_probe.py, DESIGN section 5);
+    fp64 is that exact value.  The coordinates are always compared with the fp32 oracle."""
+    for o, r, r64 in ((ours0, ref0, std_ref0), (ours1, ref1, std_ref1)):
         o = torch.as_tensor(o).cpu().double()
         r = torch.as_tensor(r).cpu().double()
         assert o.shape == r.shape, f"shape {tuple(o.shape)} vs {tuple(r.shape)}"
@@ -78,9 +96,12 @@ def check_fine(ours0, ours1, ref0, ref1):
         err = (o[:, :2] - r[:, :2]).abs().max().item()
         assert err <= COORD_TOL_PX, f"fine coordinate error {err:.3e} px > {COORD_TOL_PX}"
         if o.shape[1] > 2:
-            serr = (o[:, 2] - r[:, 2]).abs()
-            tol = STD_ATOL + STD_RTOL * r[:, 2].abs()
-            assert bool((serr <= tol).all()), f"std error {serr.max().item():.3e}"
+            s = r[:, 2] if r64 is None else torch.as_tensor(r64).cpu().double()[:, 2]
+            serr = (o[:, 2] - s).abs()
+            tol = STD_ATOL + STD_RTOL * s.abs()
+            k = int(torch.argmax(serr / tol))
+            assert bool((serr <= tol).all()), (f"std error {serr[k].item():.3e} at match {k} (ours {o[k, 2].item():.6e}, "
+                                               f"oracle {s[k].item():.6e}{'' if r64 is None else ' fp64'}, fp32 oracle {r[k, 2].item():.6e})")
 
 
 def check_windows(ours, ref, rtol=2e-5, atol=2e-5):

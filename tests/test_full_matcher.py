@@ -255,3 +255,11 @@ def test_backbone_fused_heads_equal_eager_heads():
     assert c1.dtype == torch.float32 and f1.dtype == torch.bfloat16 and c1.shape == c0.shape and f1.shape == f0.shape
     assert (c1 - c0).abs().max() <= 2e-5 * c0.abs().max()
     assert ((f1.float() - f0).abs() <= 2e-5 * f0.abs().max() + f0.abs() * 2.0 ** -8).all()
+
+
+def test_default_config_equals_the_oracle_shim():
+    """matcher.default_config (product) and reference_shims.default_config (test infrastructure) restate the same
+    demo/net_config.py values; the product no longer imports the oracle's copy."""
+    from featurematching_b200.matcher import default_config
+    from oracle import reference_shims
+    assert default_config() == reference_shims.default_config()

@@ -451,8 +451,9 @@ def test_whole_head_640x512_with_transformers_vs_oracle():
     w0, w1 = ft(w0, w1)
     fin(w0, w1, data)
     compare.check_coarse(data, ref, o64["conf_matrix"])
-    if data["b_ids"].numel() == ref["b_ids"].numel():
-        compare.check_fine(data["mkpts0_f"], data["mkpts1_f"], ref["mkpts0_f"], ref["mkpts1_f"])
+    ko, kr = compare.common_rows(data, ref)         # all of them unless a tie was tolerated
+    assert ko.numel() >= ref["b_ids"].numel() - 4
+    compare.check_fine(data["mkpts0_f"].cpu()[ko], data["mkpts1_f"].cpu()[ko], ref["mkpts0_f"][kr], ref["mkpts1_f"][kr])
     # (2) the sync-free head with the transformer inside
     head = pipeline.MatchHead(CFG, DEV, fine_transformer=ft)
     head.load_params(p)
@@ -460,9 +461,81 @@ def test_whole_head_640x512_with_transformers_vs_oracle():
     M = head.check_status(r)
     ours = {"b_ids": r.coarse.b_ids[:M], "i_ids": r.coarse.i_ids[:M], "j_ids": r.coarse.j_ids[:M],
             "mconf": r.coarse.mconf[:M], "mkpts0_c": r.coarse.mkpts0_c[:M], "mkpts1_c": r.coarse.mkpts1_c[:M]}
-    ties = compare.check_coarse(ours, ref, o64["conf_matrix"])
-    if ties == 0:
-        compare.check_fine(r.mkpts0_f[:M], r.mkpts1_f[:M], ref["mkpts0_f"], ref["mkpts1_f"])
+    compare.check_coarse(ours, ref, o64["conf_matrix"])
+    ko, kr = compare.common_rows(ours, ref)
+    assert ko.numel() >= ref["b_ids"].numel() - 4
+    compare.check_fine(r.mkpts0_f[:M].cpu()[ko], r.mkpts1_f[:M].cpu()[ko], ref["mkpts0_f"][kr], ref["mkpts1_f"][kr])
+
+
+def _oracle_fine_stage(ids, mk0, mk1, fc0, fc1, ff0, ff1, hw_i, hw_c, hw_f, p, layers, dtype=torch.float32):
+    """The oracle's fine stage (windows + merge -> fine transformer -> dual correlate) on a GIVEN match list."""
+    b, i, j = (t.cpu() for t in ids)
+    w0, w1 = mo.fine_preprocess(ff0, ff1, fc0, fc1, b, i, j, hw_c, hw_c, hw_f, 7, p, dtype)
+    w0, w1 = mo.local_feature_transformer(w0, w1, layers, CFG["fine"]["layer_names"], CFG["fine"]["nhead"], dtype=dtype)
+    return mo.fine_match(w0, w1, mk0.cpu(), mk1.cpu(), p, hw_i, hw_f, dtype=dtype)
+
+
+def _head_with_transformer(p, seed=77):
+    from featurematching_b200 import pipeline
+    torch.manual_seed(seed)
+    ft = modules.LocalFeatureTransformer(CFG["fine"]).eval()
+    layers = mo.transformer_params_from_state_dict(ft.state_dict(), 2)
+    head = pipeline.MatchHead(CFG, DEV, fine_transformer=ft.to(DEV))
+    head.load_params(p)
+    return head, layers
+
+
+def test_full_chain_1280x1024_vs_oracle():
+    """BASELINE configs[2], ONE pair, the whole chain through MatchHead.run: 20 480 + 20 480 coarse tokens, fine maps
+    64 x 512 x 640, ~18 000 matches (VERDICT r02 weak #1a: the fine stage had no test at this size).  The coarse ids at
+    this size are pinned by test_coarse_1280x1024_properties (row-streamed oracle); here they must follow the planted
+    permutation, and the fine stage is checked against the oracle run on the GPU's own match list: 1e-3 px, std within
+    STD_ATOL + STD_RTOL |std| (fine_matching_new.py:56-79 behind fine_preprocess.py:43-60 and transformer.py:78-97)."""
+    hw_c, hw_f, hw_i = (128, 160), (512, 640), (1024, 1280)
+    N = hw_c[0] * hw_c[1]
+    fc0, fc1, perm = synth.coarse_features(1, N, N, 256, 0.1, "planted", 77, sigma=1.15)
+    ff0, ff1 = synth.fine_features(1, 64, hw_f[0], hw_f[1], 4321)
+    p = synth.hot_path_params(seed=99)
+    head, layers = _head_with_transformer(p)
+    r = head.run(fc0.to(DEV), fc1.to(DEV), ff0.to(DEV), ff1.to(DEV), hw_i, hw_c, hw_c, hw_f)
+    M = head.check_status(r)
+    assert M > 14000
+    b, i, j = r.coarse.b_ids[:M].cpu(), r.coarse.i_ids[:M].cpu(), r.coarse.j_ids[:M].cpu()
+    assert torch.equal(perm[b, j], i)
+    a = ((b, i, j), r.coarse.mkpts0_c[:M], r.coarse.mkpts1_c[:M], fc0, fc1, ff0, ff1, hw_i, hw_c, hw_f, p, layers)
+    want0, want1 = _oracle_fine_stage(*a)
+    exact0, exact1 = _oracle_fine_stage(*a, dtype=torch.float64)    # the std column's reference: see compare.check_fine
+    compare.check_fine(r.mkpts0_f[:M], r.mkpts1_f[:M], want0, want1, exact0, exact1)
+    # windows at the map border exist at this size too (zero padding of F.unfold): the list reaches the outermost kept ring
+    rows, cols = torch.div(i, hw_c[1], rounding_mode="floor"), i % hw_c[1]
+    assert int(rows.min()) == 2 and int(cols.min()) == 2 and int(rows.max()) == hw_c[0] - 3 and int(cols.max()) == hw_c[1] - 3
+
+
+def test_sequence_block_320x320_with_transformer_vs_oracle():
+    """BASELINE configs[3] shape with the fine transformer inside: five consecutive-frame pairs of one 320x320 sequence
+    (overlapping views of one tensor) through MatchHead.run against the oracle -- ids under the tie rule, conf 1e-3,
+    fine coordinates 1e-3 px and std (VERDICT r02 weak #1c: only smoke() checked this chain's fine columns)."""
+    hw_c, hw_f, hw_i = (40, 40), (160, 160), (320, 320)
+    N, B = 1600, 5
+    F, perm = synth.sequence_features(B + 1, N, 256, 0.1, 5)
+    fm, _ = synth.fine_features(B + 1, 64, hw_f[0], hw_f[1], 6)
+    p = synth.hot_path_params(seed=7)
+    head, layers = _head_with_transformer(p, seed=78)
+    Fd, fmd = F.to(DEV), fm.to(DEV)
+    r = head.run(Fd[:-1], Fd[1:], fmd[:-1], fmd[1:], hw_i, hw_c, hw_c, hw_f)
+    M = head.check_status(r)
+    assert M > B * 1000
+    ours = {"b_ids": r.coarse.b_ids[:M], "i_ids": r.coarse.i_ids[:M], "j_ids": r.coarse.j_ids[:M],
+            "mconf": r.coarse.mconf[:M], "mkpts0_c": r.coarse.mkpts0_c[:M], "mkpts1_c": r.coarse.mkpts1_c[:M]}
+    f0, f1 = F[:-1].contiguous(), F[1:].contiguous()
+    ref = mo.coarse_match(f0, f1, hw_i, hw_c, hw_c)
+    o64 = mo.coarse_match(f0, f1, hw_i, hw_c, hw_c, dtype=torch.float64, return_conf=True)
+    compare.check_coarse(ours, ref, o64["conf_matrix"])
+    a = ((ours["b_ids"], ours["i_ids"], ours["j_ids"]), ours["mkpts0_c"], ours["mkpts1_c"], f0, f1,
+         fm[:-1].contiguous(), fm[1:].contiguous(), hw_i, hw_c, hw_f, p, layers)
+    want0, want1 = _oracle_fine_stage(*a)
+    exact0, exact1 = _oracle_fine_stage(*a, dtype=torch.float64)
+    compare.check_fine(r.mkpts0_f[:M], r.mkpts1_f[:M], want0, want1, exact0, exact1)
 
 
 # ------------------------------------------------------------------------------ sync-free pipeline
